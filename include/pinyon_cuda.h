@@ -1,0 +1,179 @@
+/* libpinyon_cuda — C ABI of the B200-native Monte-Carlo leaf evaluator for Pinyon.
+ *
+ * Pinyon (baskuit/pinyon) has no FFI of its own: its model boundary is a C++ type
+ * list (src/model/model.hh:8-79).  This header is the boundary a maintainer binds
+ * that type list to; include/pinyon_cuda/monte_carlo_model.hh is that binding
+ * (header-only C++23, no CUDA types).  Every entry point names the reference
+ * interface it replaces, file:line relative to the reference tree.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes; no CUDA or torch types.
+ *   - every function returning int returns PCU_OK (0) or a negative PCU_ERR_*;
+ *     nothing throws; pcu_last_error() gives a human-readable reason.
+ *   - a context is bound to one GPU and may be used by one thread at a time.
+ *   - there is NO CPU fallback: without a usable sm_100 device pcu_create fails.
+ *
+ * Semantics reproduced bit-for-bit:
+ *   prng            = libstdc++ std::mt19937 + its uniform_int<uint64_t> / generate_canonical<double,53>
+ *                     arithmetic                       src/types/random.hh:8-64
+ *   RandomTree      = default growth functions only    src/state/random-tree.hh:12-200
+ *   MoldState                                          src/state/test-states.hh:13-67
+ *   MonteCarloModel rollout / batched inference        src/model/monte-carlo-model.hh:41-96
+ */
+#ifndef PINYON_CUDA_H
+#define PINYON_CUDA_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCU_VERSION 100
+
+#define PCU_OK 0
+#define PCU_ERR_INVALID (-1)     /* bad argument (null pointer, depth 0, T > 9, rows*cols > 65535, ...) */
+#define PCU_ERR_CUDA (-2)        /* a CUDA runtime call failed */
+#define PCU_ERR_UNSUPPORTED (-3) /* legal in Pinyon but outside what the device path reproduces */
+#define PCU_ERR_NOMEM (-4)
+
+/* Where the array pointers of a batch / output live. */
+#define PCU_MEM_HOST 0   /* host memory; the call copies in and out (pinned memory is faster) */
+#define PCU_MEM_DEVICE 1 /* device memory of the context's GPU; nothing is copied */
+
+typedef struct pcu_ctx pcu_ctx;
+
+/* ---- context ------------------------------------------------------------------ */
+
+/* Create a context on CUDA device `device_id`.  Fails with PCU_ERR_CUDA if there is
+ * no such device or it is not compute capability 10.x. */
+int pcu_create(int device_id, pcu_ctx **out);
+void pcu_destroy(pcu_ctx *ctx);
+const char *pcu_last_error(const pcu_ctx *ctx);
+int pcu_version(void);
+/* Run on an existing cudaStream_t (passed as void*) instead of the context's own
+ * stream; NULL restores the private stream.  Calls stay synchronous for the caller. */
+int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream);
+/* Number of kernels launched by this context since creation (bench.py gpu_launches). */
+uint64_t pcu_kernel_launches(const pcu_ctx *ctx);
+/* Tuning knobs, mainly for benchmarks: key "ctas_per_sm" (1..8) sets the number of
+ * model-stream chunks per SM of the fused stream kernels.  Returns PCU_ERR_INVALID
+ * for unknown keys. */
+int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value);
+/* Pinned host memory for batch inputs/outputs (optional; any host pointer works). */
+void *pcu_host_alloc(pcu_ctx *ctx, size_t bytes);
+void pcu_host_free(pcu_ctx *ctx, void *p);
+
+/* ---- model PRNG -----------------------------------------------------------------
+ * Replaces MonteCarloModel::Model::device, a Types::PRNG (monte-carlo-model.hh:37),
+ * i.e. prng = seed + std::mt19937 (random.hh:8-13).
+ *
+ * PCU_MODEL_STREAM ("mode S") is the reference's batched inference verbatim
+ * (monte-carlo-model.hh:58-67): ONE engine consumed by the rollouts in index order,
+ * rollout i starting where rollout i-1 stopped.  The engine is passed in libstdc++'s
+ * own representation, 624 state words + the position 0..624 of the next word, and is
+ * advanced in place to its post-batch state, so the host model stays in lock-step
+ * with a CPU model that ran the same batch.
+ *
+ * PCU_MODEL_PER_ROLLOUT ("mode P"): rollout i runs on a fresh prng{seeds[i]}; what the
+ * reference computes when called as Model{prng{seeds[i]}}.inference(state_i). */
+#define PCU_MODEL_STREAM 0
+#define PCU_MODEL_PER_ROLLOUT 1
+
+typedef struct {
+    int32_t mode;
+    uint32_t *mt_x;        /* mode S: [624] engine words, HOST memory, updated in place */
+    uint32_t *mt_p;        /* mode S: next-word position 0..624, HOST memory, updated in place */
+    const uint64_t *seeds; /* mode P: [n] seeds, in the memory space of the batch */
+} pcu_model_rng;
+
+/* Host-side engine helpers (no GPU needed).  pcu_mt_seed == std::mt19937::seed as
+ * prng(seed) calls it (random.hh:16); pcu_mt_discard == prng::discard (random.hh:63),
+ * using polynomial jump-ahead for large n. */
+void pcu_mt_seed(uint64_t seed, uint32_t *mt_x, uint32_t *mt_p);
+int pcu_mt_discard(uint32_t *mt_x, uint32_t *mt_p, uint64_t n);
+uint32_t pcu_mt_next(uint32_t *mt_x, uint32_t *mt_p);
+
+/* ---- RandomTree batch -----------------------------------------------------------
+ * Structure-of-arrays image of n RandomTree::State objects (random-tree.hh:14-27).
+ * A per-rollout array pointer may be NULL, in which case the matching *_u scalar
+ * holds for every rollout (a batch of copies of one root needs no arrays at all).
+ *
+ *   state_seed       device.get_seed()            (random.hh:18) — the engine uses seed mod 2^32
+ *   state_pos        draws the state's device has made since seeding, INCLUDING the
+ *                    2*rows*cols*transitions of its latest get_chance_strategies()
+ *                    (ctor :31-41 or apply_actions :105-107)
+ *   transition_seed  (:15,59-61)
+ *   depth            depth_bound (:16), >= 1
+ *   payoff_bias      (:20)
+ *   rows, cols, transitions, chance_threshold = thr_p/thr_q  (:17-21) batch-uniform
+ * Only the default growth functions (:141-146) are reproduced. */
+typedef struct {
+    uint64_t n;
+    int32_t mem;
+    const uint64_t *state_seed;
+    uint64_t state_seed_u;
+    const uint32_t *state_pos;
+    uint32_t state_pos_u;
+    const uint64_t *transition_seed;
+    uint64_t transition_seed_u;
+    const uint16_t *depth;
+    uint16_t depth_u;
+    const int32_t *payoff_bias;
+    int32_t payoff_bias_u;
+    uint32_t rows, cols, transitions;
+    int32_t thr_p, thr_q;
+} pcu_rt_batch;
+
+/* MoldState batch (test-states.hh:13-24): n_actions uniform, max_depth per rollout. */
+typedef struct {
+    uint64_t n;
+    int32_t mem;
+    const uint16_t *depth;
+    uint16_t depth_u;
+    uint32_t n_actions;
+} pcu_mold_batch;
+
+/* ---- outputs ---------------------------------------------------------------------
+ * Replaces ModelOutput::value / ModelBatchOutput (monte-carlo-model.hh:6-32).
+ *   payoff_x2[i]  2 * row payoff: 0, 1 (= 1/2) or 2 (RandomTree :99-103); MoldState's
+ *                 payoff is never written by the reference, so it is 0 = (0,0).
+ *   traj          optional; 3 bytes per step (row action, col action, chance action),
+ *                 traj_stride steps reserved per rollout, zero filled past the end
+ *   traj_hash[i]  optional; FNV-1a style fold of the trajectory:
+ *                 h = 2166136261; per step h = (h ^ ((row*cols+col) | chance << 16)) * 16777619
+ *   sums[8]       optional; [0] row wins [1] draws (MoldState: all) [2] row losses [3] steps
+ *                 [4] sum of traj_hash mod 2^64, [5..7] zero.  All exact integers, so batch
+ *                 means are bit-exact: mean row value = (2*sums[0] + sums[1]) / (2.0 * n).
+ * All pointers are in out->mem space and may be NULL. */
+typedef struct {
+    int32_t mem;
+    uint8_t *payoff_x2;
+    uint8_t *traj;
+    uint32_t traj_stride;
+    uint32_t *traj_hash;
+    uint64_t *sums;
+} pcu_out;
+
+/* ---- the hot path ------------------------------------------------------------------
+ * Batched inference: replaces Model::inference(ModelBatchInput&, ModelBatchOutput&)
+ * (monte-carlo-model.hh:58-67) and, with n == 1, Model::inference(State&&, ModelOutput&)
+ * (:41-56) for RandomTree / MoldState states.  Blocks until outputs are complete. */
+int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *batch, pcu_model_rng *rng, pcu_out *out);
+int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *batch, pcu_model_rng *rng, pcu_out *out);
+
+/* Name of the kernel path the last rollout call took ("stream_table", "stream_mold",
+ * "warp_private", ...); for tests and benchmarks. */
+const char *pcu_last_path(const pcu_ctx *ctx);
+
+/* Integer-issue peak microbenchmark (eight cross-coupled chains per thread, best of
+ * `reps`, CUDA events), the roofline denominator of SURVEY.md §8(d).  variant 0: LOP3
+ * only; 1: LOP3 + SHF + IADD3 (ALU pipe); 2: LOP3 + SHF + IMAD (ALU + FMA pipes).
+ * Writes int32 thread-operations per second. */
+int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_second);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PINYON_CUDA_H */

@@ -1,0 +1,636 @@
+// sm_100a rollout kernels of libpinyon_cuda.  See DESIGN.md "Kernels".
+//
+// k_stream      fused hot path: one MT19937 model stream per CTA, generated 224 words
+//               at a time by 224 threads (the recurrence X[n] = X[n-227] ^ f(X[n-624],
+//               X[n-623]) allows 227 independent words), reduced in-register to joint
+//               action codes, staged in shared memory and consumed one rollout per
+//               thread against a shared-memory table of the (shared) state stream.
+// k_gen_codes   the same generator writing action codes to global memory, for
+//               batches the fused kernel does not take (ragged depth, private states).
+// k_warp        general path: one rollout per warp, the state's private MT19937 in
+//               shared memory, advanced 32 words per step by the warp.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "mt19937.cuh"
+
+#define PCU_FULL 0xffffffffu
+#define PCU_HASH_INIT 2166136261u
+#define PCU_HASH_MUL 16777619u
+
+constexpr int GEN_THREADS = 224;           /* 7 warps; <= 227 so one group has no internal dependency */
+constexpr int RING_WORDS = 4 * GEN_THREADS; /* 896 >= 624 + 224: four group slots */
+constexpr int STEPS_PER_GROUP = GEN_THREADS / 4; /* a step = 2 random_int = 4 words */
+
+enum { KIND_TREE = 0, KIND_MOLD = 1 };
+
+struct StreamParams {
+    uint64_t n;      /* rollouts */
+    uint64_t chunk;  /* rollouts per CTA, multiple of 224 */
+    uint32_t depth;  /* uniform depth_bound / max_depth */
+    uint32_t cols, T, gen_words;
+    ModConst mrow, mcol;
+    const uint32_t *checkpoints; /* [ctas][624] raw words preceding each CTA's first model word */
+    const uint8_t *tab;          /* state-stream table: low nibble u64%10, bits 4-5 u64%3 at each draw index */
+    uint32_t tab_base, tab_len;
+    const uint32_t *state_pos;
+    uint32_t state_pos_u;
+    const int32_t *bias;
+    int32_t bias_u;
+    double pu;
+    int32_t thr_p, thr_q;
+    const double *fq; /* fq[n * fq_w + S] = (double)(float)(n / (double)S) */
+    uint32_t fq_w;
+    uint8_t *payoff;
+    uint8_t *traj;
+    uint32_t traj_stride;
+    uint32_t *traj_hash;
+    unsigned long long *sums;
+    uint32_t *end_window; /* [624] raw words preceding the first model word after the batch */
+};
+
+__device__ __forceinline__ uint32_t hash_step(uint32_t h, uint32_t joint, uint32_t chance) {
+    return (h ^ (joint | (chance << 16))) * PCU_HASH_MUL;
+}
+
+__device__ __forceinline__ unsigned long long warp_sum_u64(unsigned long long v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(PCU_FULL, v, o);
+    return v;
+}
+
+/* Per-thread constants of the 224-wide generator: ring slots for the four phases. */
+struct GenAddr {
+    uint16_t ra[4], rb[4], rc[4], wa[4];
+    uint32_t n, m, c32; /* modulus of this lane's word: rows for words 0,1 of a step, cols for 2,3 */
+};
+
+__device__ __forceinline__ GenAddr make_gen_addr(int t, const ModConst &mrow, const ModConst &mcol) {
+    GenAddr g;
+#pragma unroll
+    for (int ph = 0; ph < 4; ++ph) {
+        const int off = GEN_THREADS * ph + t;
+        g.ra[ph] = (uint16_t)((off + 48) % RING_WORDS);  /* X[n-624] */
+        g.rb[ph] = (uint16_t)((off + 49) % RING_WORDS);  /* X[n-623] */
+        g.rc[ph] = (uint16_t)((off + 445) % RING_WORDS); /* X[n-227] */
+        g.wa[ph] = (uint16_t)((off + 672) % RING_WORDS); /* X[n]     */
+    }
+    const ModConst &mc = (t & 2) ? mcol : mrow;
+    g.n = mc.n;
+    g.m = mc.m;
+    g.c32 = mc.c32;
+    return g;
+}
+
+__device__ __forceinline__ void load_checkpoint(uint32_t *ring, const uint32_t *ckpt, int t) {
+    for (int i = t; i < MT_N; i += GEN_THREADS) ring[48 + i] = ckpt[i];
+}
+
+/* One group: every thread produces one stream word; lanes 4q..4q+3 hold the words of
+ * step q (row hi, row lo, col hi, col lo — uniform_64 draws HIGH first, random.hh:28).
+ * Returns the joint action code row*cols+col on lanes with (t & 3) == 0. */
+template <int PH>
+__device__ __forceinline__ uint32_t gen_group(uint32_t *ring, const GenAddr &g, uint32_t cols) {
+    const uint32_t a = ring[g.ra[PH]], b = ring[g.rb[PH]], c = ring[g.rc[PH]];
+    const uint32_t x = mt_twist(a, b, c);
+    ring[g.wa[PH]] = x;
+    const uint32_t z = mt_temper(x);
+    const uint32_t m = mod32(z, g.n, g.m);
+    const uint32_t lo = __shfl_down_sync(PCU_FULL, m, 1);
+    const uint32_t v = mod32(m * g.c32 + lo, g.n, g.m);
+    const uint32_t cc = __shfl_down_sync(PCU_FULL, v, 2);
+    return v * cols + cc;
+}
+
+/* The raw (untempered) word only — used by the jump-ahead extension kernel. */
+template <int PH>
+__device__ __forceinline__ uint32_t gen_raw(uint32_t *ring, const GenAddr &g) {
+    const uint32_t a = ring[g.ra[PH]], b = ring[g.rb[PH]], c = ring[g.rc[PH]];
+    const uint32_t x = mt_twist(a, b, c);
+    ring[g.wa[PH]] = x;
+    return x;
+}
+
+/* The 624 raw words preceding stream word `w_end`, counted from the start of the current
+ * 896-word-aligned generation pass (ring slot of word n' is (n' + 672) mod 896). */
+__device__ __forceinline__ void dump_window(const uint32_t *ring, uint32_t w_end, uint32_t *dst, int t) {
+    for (int i = t; i < MT_N; i += GEN_THREADS) dst[i] = ring[(w_end + 48 + i) % RING_WORDS];
+}
+
+template <int KIND, typename CodeT, bool TAB_SMEM>
+__global__ void __launch_bounds__(GEN_THREADS) k_stream(const StreamParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint32_t *ring = reinterpret_cast<uint32_t *>(smem_raw);
+    CodeT *codes = reinterpret_cast<CodeT *>(ring + RING_WORDS);
+    const int t = threadIdx.x;
+    const uint32_t d = P.depth;
+    const uint64_t first = (uint64_t)blockIdx.x * P.chunk;
+    if (first >= P.n) return;
+    const uint64_t last = (first + P.chunk < P.n) ? first + P.chunk : P.n;
+
+    const uint8_t *tab = P.tab;
+    if (KIND == KIND_TREE && TAB_SMEM) {
+        uint8_t *stab = reinterpret_cast<uint8_t *>(codes + (size_t)GEN_THREADS * d);
+        stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
+        for (uint32_t i = t; i < P.tab_len; i += GEN_THREADS) stab[i] = P.tab[i];
+        tab = stab;
+    }
+    load_checkpoint(ring, P.checkpoints + (size_t)blockIdx.x * MT_N, t);
+    const GenAddr g = make_gen_addr(t, P.mrow, P.mcol);
+    const bool writer = (t & 3) == 0;
+    const uint32_t q0 = t >> 2;
+    __syncthreads();
+
+    unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_n = 0;
+
+    for (uint64_t base = first; base < last; base += GEN_THREADS) {
+        /* ---- generate this round's steps: 4*d groups (224*d steps) for a full round, only
+         * the groups its rollouts need for the ragged last one */
+        const uint32_t live = (last - base < GEN_THREADS) ? (uint32_t)(last - base) : GEN_THREADS;
+        const uint32_t groups = (live * d + STEPS_PER_GROUP - 1) / STEPS_PER_GROUP;
+        uint32_t q = q0;
+        for (uint32_t g4 = 0; g4 < (groups >> 2); ++g4) {
+            uint32_t code;
+            code = gen_group<0>(ring, g, P.cols);
+            if (writer) codes[q] = (CodeT)code;
+            q += STEPS_PER_GROUP;
+            __syncthreads();
+            code = gen_group<1>(ring, g, P.cols);
+            if (writer) codes[q] = (CodeT)code;
+            q += STEPS_PER_GROUP;
+            __syncthreads();
+            code = gen_group<2>(ring, g, P.cols);
+            if (writer) codes[q] = (CodeT)code;
+            q += STEPS_PER_GROUP;
+            __syncthreads();
+            code = gen_group<3>(ring, g, P.cols);
+            if (writer) codes[q] = (CodeT)code;
+            q += STEPS_PER_GROUP;
+            __syncthreads();
+        }
+        if (groups & 3) { /* only ever in the batch's last round */
+            uint32_t code = gen_group<0>(ring, g, P.cols);
+            if (writer) codes[q] = (CodeT)code;
+            q += STEPS_PER_GROUP;
+            __syncthreads();
+            if ((groups & 3) > 1) {
+                code = gen_group<1>(ring, g, P.cols);
+                if (writer) codes[q] = (CodeT)code;
+                q += STEPS_PER_GROUP;
+                __syncthreads();
+            }
+            if ((groups & 3) > 2) {
+                code = gen_group<2>(ring, g, P.cols);
+                if (writer) codes[q] = (CodeT)code;
+                q += STEPS_PER_GROUP;
+                __syncthreads();
+            }
+        }
+        /* the engine state the host model must continue from: the window right after the
+         * batch's last model word (monte-carlo-model.hh:58-67 leaves `device` there) */
+        if (last == P.n && base + GEN_THREADS >= last && P.end_window) dump_window(ring, 4u * d * live, P.end_window, t);
+        /* ---- consume: thread t plays rollout base + t with steps codes[t*d .. t*d+d) */
+        const uint64_t i = base + t;
+        if (i < last) {
+            const CodeT *my = codes + (size_t)t * d;
+            uint32_t h = PCU_HASH_INIT;
+            uint32_t pay = 0;
+            uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
+            if (KIND == KIND_MOLD) {
+                for (uint32_t s = 0; s < d; ++s) {
+                    const uint32_t code = my[s];
+                    h = hash_step(h, code, 0);
+                    if (tr) {
+                        const uint32_t r = code / P.cols;
+                        tr[3 * s + 0] = (uint8_t)r;
+                        tr[3 * s + 1] = (uint8_t)(code - r * P.cols);
+                        tr[3 * s + 2] = 0;
+                    }
+                }
+                acc_d += 1;
+            } else {
+                uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
+                int bias = P.bias ? P.bias[i] : P.bias_u;
+                const uint32_t T = P.T;
+                if (T == 1) {
+                    for (uint32_t s = 0; s < d; ++s) {
+                        const uint32_t code = my[s];
+                        p += code; /* discard(row*cols + col): random-tree.hh:88-89 */
+                        bias += (int)((tab[p] >> 4) & 3u) - 1;
+                        p += 2 + P.gen_words;
+                        h = hash_step(h, code, 0);
+                        if (tr) {
+                            const uint32_t r = code / P.cols;
+                            tr[3 * s + 0] = (uint8_t)r;
+                            tr[3 * s + 1] = (uint8_t)(code - r * P.cols);
+                            tr[3 * s + 2] = 0;
+                        }
+                    }
+                } else {
+                    uint32_t gb = p - P.gen_words; /* where the current chance strategies were drawn */
+                    for (uint32_t s = 0; s < d; ++s) {
+                        const uint32_t code = my[s];
+                        const uint32_t st = code * T;
+                        const uint8_t *cell = tab + gb + 2 * st;
+                        int S = 0;
+                        for (uint32_t k = 0; k < T; ++k) {
+                            int nk = (int)(cell[2 * k] & 15u) + 1;
+                            if (nk * P.thr_q < P.thr_p * 10) nk = 0;
+                            S += nk;
+                        }
+                        const bool fallback = (S == 0);
+                        if (fallback) S = 1;
+                        double pp = P.pu;
+                        uint32_t ch = 0;
+                        for (uint32_t k = 0; k < T; ++k) {
+                            int nk = (int)(cell[2 * k] & 15u) + 1;
+                            if (nk * P.thr_q < P.thr_p * 10) nk = 0;
+                            if (fallback && k == 0) nk = 1;
+                            pp -= __ldg(P.fq + (uint32_t)nk * P.fq_w + (uint32_t)S);
+                            if (pp <= 0) {
+                                ch = k;
+                                break;
+                            }
+                        }
+                        p += st + ch;
+                        bias += (int)((tab[p] >> 4) & 3u) - 1;
+                        p += 2;
+                        gb = p;
+                        p += P.gen_words;
+                        h = hash_step(h, code, ch);
+                        if (tr) {
+                            const uint32_t r = code / P.cols;
+                            tr[3 * s + 0] = (uint8_t)r;
+                            tr[3 * s + 1] = (uint8_t)(code - r * P.cols);
+                            tr[3 * s + 2] = (uint8_t)ch;
+                        }
+                    }
+                }
+                pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
+                acc_w += (pay == 2);
+                acc_d += (pay == 1);
+                acc_l += (pay == 0);
+            }
+            if (tr)
+                for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
+            if (P.payoff) P.payoff[i] = (uint8_t)pay;
+            if (P.traj_hash) P.traj_hash[i] = h;
+            acc_h += h;
+            acc_n += 1;
+        }
+        __syncthreads();
+    }
+    if (P.sums) {
+        acc_w = warp_sum_u64(acc_w);
+        acc_d = warp_sum_u64(acc_d);
+        acc_l = warp_sum_u64(acc_l);
+        acc_h = warp_sum_u64(acc_h);
+        acc_n = warp_sum_u64(acc_n);
+        if ((t & 31) == 0) {
+            if (acc_w) atomicAdd(P.sums + 0, acc_w);
+            if (acc_d) atomicAdd(P.sums + 1, acc_d);
+            if (acc_l) atomicAdd(P.sums + 2, acc_l);
+            atomicAdd(P.sums + 3, acc_n * d);
+            atomicAdd(P.sums + 4, acc_h);
+        }
+    }
+}
+
+/* ------------------------------------------------------------------ k_gen_codes */
+
+struct GenParams {
+    uint64_t total_steps;
+    uint64_t chunk_steps; /* steps per CTA, multiple of 224 */
+    uint32_t cols;
+    ModConst mrow, mcol;
+    const uint32_t *checkpoints;
+    void *codes; /* CodeT[total_steps] */
+    uint32_t *end_window;
+};
+
+template <typename CodeT>
+__global__ void __launch_bounds__(GEN_THREADS) k_gen_codes(const GenParams P) {
+    __shared__ uint32_t ring[RING_WORDS];
+    const int t = threadIdx.x;
+    const uint64_t first = (uint64_t)blockIdx.x * P.chunk_steps;
+    if (first >= P.total_steps) return;
+    const uint64_t last = (first + P.chunk_steps < P.total_steps) ? first + P.chunk_steps : P.total_steps;
+    load_checkpoint(ring, P.checkpoints + (size_t)blockIdx.x * MT_N, t);
+    const GenAddr g = make_gen_addr(t, P.mrow, P.mcol);
+    const bool writer = (t & 3) == 0;
+    CodeT *codes = reinterpret_cast<CodeT *>(P.codes);
+    __syncthreads();
+    for (uint64_t qb = first; qb < last; qb += 4 * STEPS_PER_GROUP) { /* uniform trip count: barriers inside */
+        const uint64_t q = qb + (t >> 2);
+        const uint32_t live = (last - qb < 4 * STEPS_PER_GROUP) ? (uint32_t)(last - qb) : 4 * STEPS_PER_GROUP;
+        const uint32_t groups = (live + STEPS_PER_GROUP - 1) / STEPS_PER_GROUP; /* 1..4 */
+        uint32_t code;
+        code = gen_group<0>(ring, g, P.cols);
+        if (writer && q < last) codes[q] = (CodeT)code;
+        __syncthreads();
+        if (groups > 1) {
+            code = gen_group<1>(ring, g, P.cols);
+            if (writer && q + STEPS_PER_GROUP < last) codes[q + STEPS_PER_GROUP] = (CodeT)code;
+            __syncthreads();
+        }
+        if (groups > 2) {
+            code = gen_group<2>(ring, g, P.cols);
+            if (writer && q + 2 * STEPS_PER_GROUP < last) codes[q + 2 * STEPS_PER_GROUP] = (CodeT)code;
+            __syncthreads();
+        }
+        if (groups > 3) {
+            code = gen_group<3>(ring, g, P.cols);
+            if (writer && q + 3 * STEPS_PER_GROUP < last) codes[q + 3 * STEPS_PER_GROUP] = (CodeT)code;
+            __syncthreads();
+        }
+        if (last == P.total_steps && qb + 4 * STEPS_PER_GROUP >= last && P.end_window)
+            dump_window(ring, 4u * live, P.end_window, t);
+    }
+}
+
+/* ----------------------------------------------------------------------- k_warp */
+
+struct WarpParams {
+    uint64_t n;
+    uint32_t rows, cols, T, gen_words;
+    ModConst mrow, mcol;
+    const uint64_t *state_seed;
+    uint64_t state_seed_u;
+    const uint32_t *state_pos;
+    uint32_t state_pos_u;
+    const uint64_t *tseed;
+    uint64_t tseed_u;
+    const uint16_t *depth;
+    uint16_t depth_u;
+    const int32_t *bias;
+    int32_t bias_u;
+    int32_t thr_p, thr_q;
+    const double *fq;
+    uint32_t fq_w;
+    const uint64_t *model_seeds;  /* mode P */
+    const void *codes;            /* mode S: joint action codes */
+    const uint64_t *step_off;     /* mode S: first step of rollout i (null: i * depth_u) */
+    int32_t code_u16;
+    uint8_t *payoff;
+    uint8_t *traj;
+    uint32_t traj_stride;
+    uint32_t *traj_hash;
+    unsigned long long *sums;
+};
+
+/* A private MT19937 held in shared memory by one warp.  x[] is libstdc++'s state
+ * array; base is the draw index of x[0] (-624 while x still holds the seeded array). */
+struct WarpMT {
+    uint32_t *x;
+    long long base;
+};
+
+__device__ __forceinline__ void wmt_twist(WarpMT &e, int lane) {
+#pragma unroll 1
+    for (int sub = 0; sub < 20; ++sub) {
+        const int k = sub * 32 + lane;
+        uint32_t a = 0, b = 0, c = 0;
+        if (k < MT_N) {
+            a = e.x[k];
+            b = e.x[k + 1 == MT_N ? 0 : k + 1];
+            c = e.x[k + MT_M >= MT_N ? k - MT_LAG : k + MT_M];
+        }
+        __syncwarp();
+        if (k < MT_N) e.x[k] = mt_twist(a, b, c);
+        __syncwarp();
+    }
+    e.base += MT_N;
+}
+
+/* Tempered draw number `abs` for every active lane.  Draws are requested in
+ * non-decreasing order, so lanes that cannot be served yet wait for the next block. */
+__device__ __forceinline__ uint32_t wmt_fetch(WarpMT &e, long long abs, bool active, int lane) {
+    uint32_t val = 0;
+    bool done = !active;
+    for (;;) {
+        const long long off = abs - e.base;
+        if (!done && off < MT_N) {
+            val = mt_temper(e.x[off]);
+            done = true;
+        }
+        if (__all_sync(PCU_FULL, done)) break;
+        wmt_twist(e, lane);
+    }
+    return val;
+}
+
+template <int KIND, int MODE>
+__global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31;
+    const int wib = threadIdx.x >> 5;
+    const int warps_per_block = blockDim.x >> 5;
+    constexpr int ENGINES = (KIND == KIND_TREE ? 1 : 0) + (MODE == 1 ? 1 : 0);
+    uint32_t *mine = reinterpret_cast<uint32_t *>(smem_raw) + (size_t)wib * MT_N * (ENGINES ? ENGINES : 1);
+    uint32_t *xs = mine;                                       /* state engine */
+    uint32_t *xm = mine + (KIND == KIND_TREE ? MT_N : 0);      /* model engine (mode P) */
+    const ModConst m10 = {10u, 429496729u, 6u};
+    const ModConst m3 = {3u, 1431655765u, 1u};
+
+    unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_s = 0;
+    const uint64_t warp0 = (uint64_t)blockIdx.x * warps_per_block + wib;
+    const uint64_t stride = (uint64_t)gridDim.x * warps_per_block;
+
+    for (uint64_t i = warp0; i < P.n; i += stride) {
+        const uint32_t d = P.depth ? P.depth[i] : P.depth_u;
+        /* ---- seed: lane 0 the state engine, lane 1 the model engine, lane 2 the
+         * throw-away prng{transition_seed} of random-tree.hh:118 (only its first two
+         * draws are ever used, and they are the same every step). */
+        uint32_t v = 0;
+        if (KIND == KIND_TREE) {
+            const uint64_t ss = P.state_seed ? P.state_seed[i] : P.state_seed_u;
+            const uint64_t ts = P.tseed ? P.tseed[i] : P.tseed_u;
+            v = (lane == 2) ? (uint32_t)ts : (uint32_t)ss;
+        }
+        if (MODE == 1 && lane == 1) v = (uint32_t)P.model_seeds[i];
+        uint32_t *dst = nullptr;
+        if (KIND == KIND_TREE && lane == 0) dst = xs;
+        if (MODE == 1 && lane == 1) dst = xm;
+        const uint32_t t0 = v;
+        uint32_t t1 = 0, t2 = 0, t397 = 0, t398 = 0;
+        if (dst) dst[0] = v;
+#pragma unroll 4
+        for (uint32_t k = 1; k < MT_N; ++k) {
+            v = mt_init_step(v, k);
+            if (dst) dst[k] = v;
+            if (k == 1) t1 = v;
+            if (k == 2) t2 = v;
+            if (k == 397) t397 = v;
+            if (k == 398) t398 = v;
+        }
+        double pu = 0.0;
+        if (KIND == KIND_TREE && P.T > 1) {
+            const uint32_t o0 = mt_temper(mt_twist(t0, t1, t397));
+            const uint32_t o1 = mt_temper(mt_twist(t1, t2, t398));
+            pu = prng_uniform_from_words(o0, o1);
+            pu = __shfl_sync(PCU_FULL, pu, 2);
+        }
+        __syncwarp();
+        WarpMT es = {xs, -(long long)MT_N};
+        WarpMT em = {xm, -(long long)MT_N};
+
+        long long cur = 0;
+        int bias = 0;
+        if (KIND == KIND_TREE) {
+            cur = (long long)(P.state_pos ? P.state_pos[i] : P.state_pos_u) - (long long)P.gen_words;
+            bias = P.bias ? P.bias[i] : P.bias_u;
+        }
+        const uint64_t soff = (MODE == 0) ? (P.step_off ? P.step_off[i] : i * (uint64_t)P.depth_u) : 0;
+        uint32_t h = PCU_HASH_INIT;
+        uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
+
+        for (uint32_t s = 0; s < d; ++s) {
+            uint32_t r, c;
+            if (MODE == 0) {
+                const uint32_t code = P.code_u16 ? (uint32_t)((const uint16_t *)P.codes)[soff + s]
+                                                 : (uint32_t)((const uint8_t *)P.codes)[soff + s];
+                r = code / P.cols;
+                c = code - r * P.cols;
+            } else {
+                /* lanes 0..3 draw the four model words of this step (monte-carlo-model.hh:89-90) */
+                const uint32_t w = wmt_fetch(em, 4ll * s + lane, lane < 4, lane);
+                const ModConst &mc = (lane & 2) ? P.mcol : P.mrow;
+                const uint32_t m = mod32(w, mc.n, mc.m);
+                const uint32_t lo = __shfl_down_sync(PCU_FULL, m, 1);
+                const uint32_t vv = mod32(m * mc.c32 + lo, mc.n, mc.m);
+                r = __shfl_sync(PCU_FULL, vv, 0);
+                c = __shfl_sync(PCU_FULL, vv, 2);
+            }
+            const uint32_t joint = r * P.cols + c;
+            uint32_t ch = 0;
+            if (KIND == KIND_TREE) {
+                const uint32_t T = P.T;
+                const uint32_t st = joint * T;
+                if (T > 1) {
+                    /* lanes 0..2T-1 read the 2T words the chosen cell's strategies were drawn
+                     * from (random-tree.hh:169); lane k then owns transition k. */
+                    const uint32_t w = wmt_fetch(es, cur + 2ll * st + lane, lane < (int)(2 * T), lane);
+                    const uint32_t hi = __shfl_sync(PCU_FULL, w, (2 * lane) & 31);
+                    const uint32_t lo = __shfl_sync(PCU_FULL, w, (2 * lane + 1) & 31);
+                    int nk = 0;
+                    if (lane < (int)T) {
+                        nk = (int)mod64(hi, lo, m10) + 1;
+                        if (nk * P.thr_q < P.thr_p * 10) nk = 0;
+                    }
+                    int S = nk;
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(PCU_FULL, S, o);
+                    if (S == 0) {
+                        if (lane == 0) nk = 1;
+                        S = 1;
+                    }
+                    double pp = pu;
+                    for (uint32_t k = 0; k < T; ++k) {
+                        const int n_k = __shfl_sync(PCU_FULL, nk, k);
+                        pp -= __ldg(P.fq + (uint32_t)n_k * P.fq_w + (uint32_t)S);
+                        if (pp <= 0) {
+                            ch = k;
+                            break;
+                        }
+                    }
+                }
+                cur += (long long)P.gen_words + st + ch;
+                const uint32_t w = wmt_fetch(es, cur + lane, lane < 2, lane);
+                const uint32_t hi = __shfl_sync(PCU_FULL, w, 0);
+                const uint32_t lo = __shfl_sync(PCU_FULL, w, 1);
+                bias += (int)mod64(hi, lo, m3) - 1;
+                cur += 2;
+            }
+            h = hash_step(h, joint, ch);
+            if (tr && lane == 0) {
+                tr[3 * s + 0] = (uint8_t)r;
+                tr[3 * s + 1] = (uint8_t)c;
+                tr[3 * s + 2] = (uint8_t)ch;
+            }
+        }
+        uint32_t pay = 0;
+        if (KIND == KIND_TREE) pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
+        if (lane == 0) {
+            if (tr)
+                for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
+            if (P.payoff) P.payoff[i] = (uint8_t)pay;
+            if (P.traj_hash) P.traj_hash[i] = h;
+            if (KIND == KIND_TREE) {
+                acc_w += (pay == 2);
+                acc_d += (pay == 1);
+                acc_l += (pay == 0);
+            } else {
+                acc_d += 1;
+            }
+            acc_h += h;
+            acc_s += d;
+        }
+        __syncwarp();
+    }
+    if (P.sums && lane == 0) {
+        if (acc_w) atomicAdd(P.sums + 0, acc_w);
+        if (acc_d) atomicAdd(P.sums + 1, acc_d);
+        if (acc_l) atomicAdd(P.sums + 2, acc_l);
+        if (acc_s) atomicAdd(P.sums + 3, acc_s);
+        if (acc_h) atomicAdd(P.sums + 4, acc_h);
+    }
+}
+
+/* ------------------------------------------------------- integer-issue peak probe */
+
+/* VARIANT 0: LOP3 only; 1: LOP3 + SHF + IADD3 (all ALU pipe); 2: LOP3 + SHF + IMAD
+ * (ALU + FMA pipes).  Eight chains per thread, cross-coupled so that no two
+ * operations can be folded into one; 3 ops per chain per unrolled step. */
+__device__ __forceinline__ uint32_t op_lop3(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE8;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t op_shf(uint32_t a, uint32_t b) {
+    uint32_t d;
+    asm("shf.l.wrap.b32 %0, %1, %2, 7;" : "=r"(d) : "r"(a), "r"(b));
+    return d;
+}
+__device__ __forceinline__ uint32_t op_iadd3(uint32_t a, uint32_t b, uint32_t c) { return a + b + c; }
+__device__ __forceinline__ uint32_t op_imad(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+constexpr int INT_PEAK_OPS_PER_ITER = 4 * 8 * 3;
+
+template <int VARIANT>
+__global__ void __launch_bounds__(256) k_int_peak(uint32_t *out, uint32_t seed, int iters) {
+    uint32_t a[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = seed + threadIdx.x * 8 + j + blockIdx.x * 2048;
+    const uint32_t k1 = seed | 1u;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                const uint32_t nb = a[(j + 3) & 7];
+                if (VARIANT == 0) {
+                    a[j] = op_lop3(a[j], nb, k1);
+                    a[j] = op_lop3(a[j], k1, nb);
+                    a[j] = op_lop3(nb, a[j], k1);
+                } else if (VARIANT == 1) {
+                    a[j] = op_lop3(a[j], nb, k1);
+                    a[j] = op_shf(a[j], nb);
+                    a[j] = op_iadd3(a[j], nb, k1);
+                } else {
+                    a[j] = op_lop3(a[j], nb, k1);
+                    a[j] = op_shf(a[j], nb);
+                    a[j] = op_imad(a[j], k1, nb);
+                }
+            }
+        }
+    }
+    uint32_t r = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r ^= a[j];
+    if (r == 0x12345678u) out[blockIdx.x * blockDim.x + threadIdx.x] = r;
+}

@@ -1,0 +1,80 @@
+// MT19937 and Pinyon prng arithmetic shared by host and device code of libpinyon_cuda.
+//
+// Restates libstdc++'s std::mt19937 (the engine inside Pinyon's prng,
+// src/types/random.hh:8-13) as a LINEAR stream: X[0..623] is the seeded array,
+// X[n] = X[n-227] ^ twist(X[n-624], X[n-623]) for n >= 624, and draw number m of the
+// engine (0-based) is temper(X[624 + m]).  libstdc++'s in-place 624-word refill
+// (bits/random.tcc _M_gen_rand) computes exactly this sequence, block by block.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define PCU_HD __host__ __device__ __forceinline__
+#else
+#define PCU_HD inline
+#endif
+
+#define MT_N 624
+#define MT_M 397
+#define MT_LAG (MT_N - MT_M) /* 227: X[n] depends on X[n-227] */
+
+/* a = X[n-624], b = X[n-623], c = X[n-227] */
+PCU_HD uint32_t mt_twist(uint32_t a, uint32_t b, uint32_t c) {
+    const uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
+    return c ^ (y >> 1) ^ ((b & 1u) ? 0x9908b0dfu : 0u);
+}
+
+PCU_HD uint32_t mt_temper(uint32_t y) {
+    y ^= y >> 11;
+    y ^= (y << 7) & 0x9d2c5680u;
+    y ^= (y << 15) & 0xefc60000u;
+    y ^= y >> 18;
+    return y;
+}
+
+/* one step of std::mt19937::seed's initialisation chain */
+PCU_HD uint32_t mt_init_step(uint32_t prev, uint32_t i) { return 1812433253u * (prev ^ (prev >> 30)) + i; }
+
+/* x mod n for 32-bit x, n >= 1, with m = floor(2^32 / n) (m = 0xffffffff for n = 1):
+ * q = mulhi(x, m) is floor(x/n) or one less, so r = x - q*n lies in [0, 2n). */
+struct ModConst {
+    uint32_t n, m, c32; /* c32 = 2^32 mod n */
+};
+
+inline ModConst make_mod_const(uint32_t n) {
+    ModConst c;
+    c.n = n;
+    c.m = (n <= 1) ? 0xffffffffu : (uint32_t)(0x100000000ull / n);
+    c.c32 = (n <= 1) ? 0u : (uint32_t)(0x100000000ull % n);
+    return c;
+}
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ uint32_t mod32(uint32_t x, uint32_t n, uint32_t m) {
+    const uint32_t q = __umulhi(x, m);
+    const uint32_t r = x - q * n;
+    return min(r, r - n);
+}
+/* (hi:lo) mod n == prng::random_int(n) for the u64 uniform_64() = hi<<32 | lo
+ * (random.hh:26,28); valid for n <= 65536. */
+__device__ __forceinline__ uint32_t mod64(uint32_t hi, uint32_t lo, const ModConst &c) {
+    const uint32_t a = mod32(hi, c.n, c.m);
+    const uint32_t b = mod32(lo, c.n, c.m);
+    return mod32(a * c.c32 + b, c.n, c.m);
+}
+/* prng::uniform() (random.hh:23): generate_canonical<double,53> over a 32-bit engine;
+ * first draw is the LOW word; one rounding (in the add); clamp below 1. */
+__device__ __forceinline__ double prng_uniform_from_words(uint32_t first, uint32_t second) {
+    const double s = __dadd_rn((double)first, __dmul_rn((double)second, 4294967296.0));
+    double r = __dmul_rn(s, 5.421010862427522170037e-20); /* exact 2^-64 */
+    if (r >= 1.0) r = 0.99999999999999988897769753748; /* nextafter(1, 0) */
+    return r;
+}
+#endif
+
+inline double prng_uniform_from_words_host(uint32_t first, uint32_t second) {
+    volatile double s = (double)first + (double)second * 4294967296.0;
+    double r = s / 18446744073709551616.0;
+    if (r >= 1.0) r = 0.99999999999999988897769753748;
+    return r;
+}

@@ -1,0 +1,894 @@
+// libpinyon_cuda — C ABI implementation (include/pinyon_cuda.h) over the sm_100a
+// kernels of kernels.cuh.  Host logic only: validation, staging, path selection,
+// model-stream checkpoints, launches.  No CPU fallback exists anywhere in this file:
+// every rollout is computed by a CUDA kernel or the call fails.
+#include "../../include/pinyon_cuda.h"
+
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "mt_jump.h"
+
+namespace {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t cap = 0;
+    cudaError_t ensure(size_t bytes) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMalloc(&p, want);
+        if (e == cudaSuccess) cap = want;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+enum BufId {
+    B_STATE_SEED, B_STATE_POS, B_TSEED, B_DEPTH, B_BIAS, B_MSEED, B_PAYOFF, B_TRAJ, B_HASH, B_SUMS,
+    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_COUNT
+};
+
+}  // namespace
+
+struct pcu_ctx {
+    int device = 0;
+    int sms = 0;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    std::string err;
+    std::string path;
+    uint64_t launches = 0;
+    int ctas_per_sm = 4;
+    int force_general = 0;
+    int host_checkpoints = 0; /* test hook: brute-force checkpoints on the host instead of the jump kernels */
+    DevBuf buf[B_COUNT];
+    uint32_t *pin_small = nullptr; /* pinned staging: engine window out */
+    bool engine_pending = false;    /* pin_small holds the post-batch engine window */
+    /* cached state-stream table */
+    struct {
+        bool valid = false;
+        uint64_t seed = 0;
+        uint32_t base = 0, len = 0;
+    } tab_key;
+    /* cached fq table */
+    uint32_t fq_w = 0;
+    MtJump jump; /* host polynomials + device images for the model-stream jump-ahead */
+};
+
+namespace {
+
+int fail(pcu_ctx *ctx, int code, const char *fmt, ...) {
+    if (ctx) {
+        char tmp[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(tmp, sizeof(tmp), fmt, ap);
+        va_end(ap);
+        ctx->err = tmp;
+    }
+    return code;
+}
+
+#define CU(call)                                                                                      \
+    do {                                                                                              \
+        cudaError_t e__ = (call);                                                                     \
+        if (e__ != cudaSuccess)                                                                       \
+            return fail(ctx, PCU_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e__),   \
+                        __FILE__, __LINE__);                                                          \
+    } while (0)
+
+/* ---------------------------------------------------------------- host engine */
+
+void host_mt_seed(uint64_t seed, uint32_t *x, uint32_t *p) {
+    x[0] = (uint32_t)seed;
+    for (uint32_t i = 1; i < MT_N; ++i) x[i] = mt_init_step(x[i - 1], i);
+    *p = MT_N;
+}
+
+void host_mt_refill(uint32_t *x) {
+    for (uint32_t k = 0; k < MT_N; ++k)
+        x[k] = mt_twist(x[k], x[(k + 1) % MT_N], x[(k + MT_M) % MT_N]);
+}
+
+/* The 624 raw words preceding the engine's next draw ("window").  libstdc++ keeps a
+ * whole refilled block x[0..623] and the position p of the next word, so for p < 624 the
+ * window starts 624 - p words BEFORE the block; those words were overwritten by the
+ * in-place refill and are recovered by running the recurrence backwards: from
+ * v = X[n] ^ X[n-227] = (y >> 1) ^ (lsb(y) ? 0x9908b0df : 0), y = msb(X[n-624]) | low31(X[n-623]),
+ * the top bit of v is lsb(y) (the constant has its top bit set, y >> 1 has not). */
+void host_window_from_engine(const uint32_t *x, uint32_t p, uint32_t *win) {
+    if (p >= MT_N) {
+        memcpy(win, x, sizeof(uint32_t) * MT_N);
+        return;
+    }
+    const uint32_t r = MT_N - p; /* words to recover in front of the block */
+    std::vector<uint32_t> y(r + MT_N, 0);
+    memcpy(y.data() + r, x, sizeof(uint32_t) * MT_N);
+    /* y[i] = X[a - r + i]; step n (index into y) yields low31(y[n-623]) and msb(y[n-624]) */
+    for (uint32_t n = r + MT_N - 1; n + 1 >= MT_N; --n) { /* n >= 623 */
+        uint32_t v = y[n] ^ y[n - MT_LAG];
+        uint32_t yy;
+        if (v & 0x80000000u)
+            yy = ((v ^ 0x9908b0dfu) << 1) | 1u;
+        else
+            yy = v << 1;
+        if (n >= MT_N - 1 && n - (MT_N - 1) < r) y[n - (MT_N - 1)] = (y[n - (MT_N - 1)] & 0x80000000u) | (yy & 0x7fffffffu);
+        if (n >= MT_N && n - MT_N < r) y[n - MT_N] = (y[n - MT_N] & 0x7fffffffu) | (yy & 0x80000000u);
+        if (n == MT_N - 1) break;
+    }
+    memcpy(win, y.data(), sizeof(uint32_t) * MT_N);
+}
+
+/* Advance a window by `words` draws by plain stepping (O(words)). */
+void host_window_advance(uint32_t *win, uint64_t words) {
+    std::vector<uint32_t> ring(2 * MT_N);
+    memcpy(ring.data(), win, sizeof(uint32_t) * MT_N);
+    /* circular buffer of 624: position h is the oldest word */
+    uint32_t *x = ring.data();
+    uint32_t h = 0;
+    for (uint64_t i = 0; i < words; ++i) {
+        const uint32_t a = x[h], b = x[(h + 1) % MT_N], c = x[(h + MT_M) % MT_N];
+        x[h] = mt_twist(a, b, c);
+        h = (h + 1) % MT_N;
+    }
+    std::vector<uint32_t> out(MT_N);
+    for (uint32_t i = 0; i < MT_N; ++i) out[i] = x[(h + i) % MT_N];
+    memcpy(win, out.data(), sizeof(uint32_t) * MT_N);
+}
+
+/* ------------------------------------------------------- state-stream table */
+
+/* tab[j] describes draw index base + j of prng{seed}: low nibble = u64 % 10, bits
+ * 4-5 = u64 % 3, where u64 = (draw[j] << 32) | draw[j+1] (random.hh:26,28). */
+void host_build_table(uint64_t seed, uint32_t base, uint32_t len, std::vector<uint8_t> &tab) {
+    std::vector<uint32_t> x(MT_N);
+    uint32_t p;
+    host_mt_seed(seed, x.data(), &p);
+    const uint64_t need = (uint64_t)base + len + 1;
+    std::vector<uint32_t> w(len + 1);
+    uint64_t idx = 0;
+    while (idx < need) {
+        host_mt_refill(x.data());
+        for (uint32_t k = 0; k < MT_N && idx < need; ++k, ++idx)
+            if (idx >= base) w[idx - base] = mt_temper(x[k]);
+    }
+    tab.resize(len);
+    for (uint32_t j = 0; j < len; ++j) {
+        const uint64_t u = ((uint64_t)w[j] << 32) | w[j + 1];
+        tab[j] = (uint8_t)((u % 10) | ((u % 3) << 4));
+    }
+}
+
+double host_uniform_from_seed(uint64_t seed) {
+    uint32_t x0 = (uint32_t)seed, v = x0, x1 = 0, x2 = 0, x397 = 0, x398 = 0;
+    for (uint32_t i = 1; i <= 398; ++i) {
+        v = mt_init_step(v, i);
+        if (i == 1) x1 = v;
+        if (i == 2) x2 = v;
+        if (i == 397) x397 = v;
+        if (i == 398) x398 = v;
+    }
+    const uint32_t o0 = mt_temper(mt_twist(x0, x1, x397));
+    const uint32_t o1 = mt_temper(mt_twist(x1, x2, x398));
+    return prng_uniform_from_words_host(o0, o1);
+}
+
+/* fq[n * w + S] = (double)(float)((double)n / (double)S): the value random-tree.hh:123
+ * subtracts — math::to_double returns float (math.hh:30-33) — for a strategy entry
+ * n/S (equal to the reference's reduced fraction p/(double)q: one correctly rounded
+ * divide of the same rational). */
+void host_build_fq(uint32_t T, std::vector<double> &fq, uint32_t *w_out) {
+    const uint32_t w = 10 * T + 1;
+    fq.assign((size_t)11 * w, 0.0);
+    for (uint32_t n = 0; n <= 10; ++n)
+        for (uint32_t S = 1; S < w; ++S) {
+            volatile double q = (double)n / (double)S;
+            volatile float f = (float)q;
+            fq[(size_t)n * w + S] = (double)f;
+        }
+    *w_out = w;
+}
+
+template <typename T>
+int stage_in(pcu_ctx *ctx, int mem, const T *src, uint64_t n, BufId id, const T **dev_out) {
+    if (!src) {
+        *dev_out = nullptr;
+        return PCU_OK;
+    }
+    if (mem == PCU_MEM_DEVICE) {
+        *dev_out = src;
+        return PCU_OK;
+    }
+    CU(ctx->buf[id].ensure(sizeof(T) * n));
+    CU(cudaMemcpyAsync(ctx->buf[id].p, src, sizeof(T) * n, cudaMemcpyHostToDevice, ctx->stream));
+    *dev_out = reinterpret_cast<const T *>(ctx->buf[id].p);
+    return PCU_OK;
+}
+
+template <typename T>
+int stage_out(pcu_ctx *ctx, int mem, T *dst, uint64_t count, BufId id, T **dev_out) {
+    if (!dst) {
+        *dev_out = nullptr;
+        return PCU_OK;
+    }
+    if (mem == PCU_MEM_DEVICE) {
+        *dev_out = dst;
+        return PCU_OK;
+    }
+    CU(ctx->buf[id].ensure(sizeof(T) * count));
+    *dev_out = reinterpret_cast<T *>(ctx->buf[id].p);
+    return PCU_OK;
+}
+
+template <typename T>
+int copy_back(pcu_ctx *ctx, int mem, T *dst, const T *dev, uint64_t count) {
+    if (!dst || mem == PCU_MEM_DEVICE) return PCU_OK;
+    CU(cudaMemcpyAsync(dst, dev, sizeof(T) * count, cudaMemcpyDeviceToHost, ctx->stream));
+    return PCU_OK;
+}
+
+struct OutDev {
+    uint8_t *payoff = nullptr;
+    uint8_t *traj = nullptr;
+    uint32_t *hash = nullptr;
+    unsigned long long *sums = nullptr;
+};
+
+int prepare_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, OutDev &od) {
+    int rc;
+    if ((rc = stage_out(ctx, out->mem, out->payoff_x2, n, B_PAYOFF, &od.payoff))) return rc;
+    if ((rc = stage_out(ctx, out->mem, out->traj, n * (uint64_t)out->traj_stride * 3, B_TRAJ, &od.traj)))
+        return rc;
+    if ((rc = stage_out(ctx, out->mem, out->traj_hash, n, B_HASH, &od.hash))) return rc;
+    uint64_t *s = nullptr;
+    if ((rc = stage_out(ctx, out->mem, out->sums, (uint64_t)8, B_SUMS, &s))) return rc;
+    od.sums = reinterpret_cast<unsigned long long *>(s);
+    if (od.sums) CU(cudaMemsetAsync(od.sums, 0, 8 * sizeof(uint64_t), ctx->stream));
+    return PCU_OK;
+}
+
+int finish_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od) {
+    int rc;
+    if ((rc = copy_back(ctx, out->mem, out->payoff_x2, od.payoff, n))) return rc;
+    if ((rc = copy_back(ctx, out->mem, out->traj, od.traj, n * (uint64_t)out->traj_stride * 3))) return rc;
+    if ((rc = copy_back(ctx, out->mem, out->traj_hash, od.hash, n))) return rc;
+    if ((rc = copy_back(ctx, out->mem, out->sums, reinterpret_cast<const uint64_t *>(od.sums), (uint64_t)8)))
+        return rc;
+    CU(cudaStreamSynchronize(ctx->stream));
+    return PCU_OK;
+}
+
+void engine_from_window(const uint32_t *win, uint32_t *mt_x, uint32_t *mt_p);
+
+int finish_all(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od, pcu_model_rng *rng) {
+    int rc = finish_out(ctx, out, n, od);
+    if (rc) {
+        ctx->engine_pending = false;
+        return rc;
+    }
+    if (ctx->engine_pending) {
+        engine_from_window(ctx->pin_small, rng->mt_x, rng->mt_p);
+        ctx->engine_pending = false;
+    }
+    return PCU_OK;
+}
+
+/* ------------------------------------------------ model-stream checkpoints */
+
+/* Fill B_CKPT with `count` windows: window c holds the 624 raw words preceding model
+ * draw number c * unit_words * 2^j, counted from the engine's next draw. */
+int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t count, uint64_t unit_words, int j) {
+    std::vector<uint32_t> win(MT_N);
+    host_window_from_engine(mt_x, mt_p, win.data());
+    CU(ctx->buf[B_CKPT].ensure(sizeof(uint32_t) * MT_N * (count + 1)));
+    CU(ctx->buf[B_ENDWIN].ensure(sizeof(uint32_t) * MT_N));
+    uint32_t *d_ck = reinterpret_cast<uint32_t *>(ctx->buf[B_CKPT].p);
+    if (ctx->host_checkpoints && count > 1) {
+        /* test hook: plain stepping on the host, the definition the jump kernels must match */
+        const uint64_t stride = unit_words << j;
+        std::vector<uint32_t> all((size_t)MT_N * count);
+        for (uint64_t c = 0; c < count; ++c) {
+            memcpy(all.data() + (size_t)MT_N * c, win.data(), sizeof(uint32_t) * MT_N);
+            if (c + 1 < count) host_window_advance(win.data(), stride);
+        }
+        CU(cudaMemcpyAsync(d_ck, all.data(), sizeof(uint32_t) * MT_N * count, cudaMemcpyHostToDevice, ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream)); /* `all` is pageable and about to go out of scope */
+        return PCU_OK;
+    }
+    std::string jerr;
+    if (ctx->jump.run(ctx->stream, win.data(), count, unit_words, j, d_ck, &ctx->launches, &jerr) != 0)
+        return fail(ctx, PCU_ERR_CUDA, "jump-ahead failed: %s", jerr.c_str());
+    return PCU_OK;
+}
+
+void engine_from_window(const uint32_t *win, uint32_t *mt_x, uint32_t *mt_p) {
+    /* (window, 624) is an engine state equivalent to libstdc++'s own after the same
+     * draws: its next refill computes the same block. */
+    memcpy(mt_x, win, sizeof(uint32_t) * MT_N);
+    *mt_p = MT_N;
+}
+
+int fetch_end_window(pcu_ctx *ctx) {
+    CU(cudaMemcpyAsync(ctx->pin_small, ctx->buf[B_ENDWIN].p, sizeof(uint32_t) * MT_N, cudaMemcpyDeviceToHost,
+                       ctx->stream));
+    ctx->engine_pending = true;
+    return PCU_OK;
+}
+
+/* Work is cut into 224 * 2^j units per CTA so that every checkpoint stride is one of the
+ * cached polynomials x^(unit * 2^j); j is the smallest that fits the CTA budget. */
+int pick_shift(uint64_t units224, int sms, int ctas_per_sm) {
+    const uint64_t budget = (uint64_t)sms * ctas_per_sm;
+    int j = 0;
+    while (((units224 + (1ull << j) - 1) >> j) > budget) ++j;
+    return j;
+}
+
+template <int KIND, typename CodeT>
+int launch_stream(pcu_ctx *ctx, const StreamParams &P, uint64_t ctas, bool tab_smem, size_t smem) {
+    auto kern = tab_smem ? k_stream<KIND, CodeT, true> : k_stream<KIND, CodeT, false>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)ctas, GEN_THREADS, smem, ctx->stream>>>(P);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
+
+constexpr size_t SMEM_LIMIT = 200 * 1024;
+
+/* Fused path (mode S, uniform depth, shared or absent state stream). */
+template <int KIND>
+int run_stream(pcu_ctx *ctx, StreamParams &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od) {
+    const uint64_t n = P.n;
+    const uint64_t rounds = (n + GEN_THREADS - 1) / GEN_THREADS;
+    const int j = pick_shift(rounds, ctx->sms, ctx->ctas_per_sm);
+    P.chunk = (uint64_t)GEN_THREADS << j;
+    const uint64_t ctas = (n + P.chunk - 1) / P.chunk;
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, ctas, 4ull * P.depth * GEN_THREADS, j);
+    if (rc) return rc;
+    P.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
+    P.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
+    P.payoff = od.payoff;
+    P.traj = od.traj;
+    P.traj_hash = od.hash;
+    P.sums = od.sums;
+    const bool code8 = (uint64_t)rows * P.cols <= 256;
+    const size_t code_bytes = (size_t)GEN_THREADS * P.depth * (code8 ? 1 : 2);
+    size_t smem = RING_WORDS * 4 + code_bytes + 16;
+    bool tab_smem = false;
+    if (KIND == KIND_TREE && smem + P.tab_len + 16 <= SMEM_LIMIT) {
+        tab_smem = true;
+        smem += P.tab_len + 16;
+    }
+    if (smem > SMEM_LIMIT) return fail(ctx, PCU_ERR_UNSUPPORTED, "depth %u needs %zu B of shared memory", P.depth, smem);
+    if (code8)
+        rc = launch_stream<KIND, uint8_t>(ctx, P, ctas, tab_smem, smem);
+    else
+        rc = launch_stream<KIND, uint16_t>(ctx, P, ctas, tab_smem, smem);
+    if (rc) return rc;
+    return fetch_end_window(ctx);
+}
+
+/* General path helper: joint action codes for every step of a mode-S batch. */
+int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, pcu_model_rng *rng, bool *code16) {
+    const bool c16 = (uint64_t)rows * cols > 256;
+    *code16 = c16;
+    const uint64_t units = (total_steps + GEN_THREADS - 1) / GEN_THREADS;
+    int j = pick_shift(units, ctx->sms, ctx->ctas_per_sm);
+    if (j < 6) j = 6; /* small batches: few CTAs, few jumps */
+    const uint64_t chunk = (uint64_t)GEN_THREADS << j;
+    uint64_t ctas = (total_steps + chunk - 1) / chunk;
+    if (ctas == 0) ctas = 1;
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, ctas, 4ull * GEN_THREADS, j);
+    if (rc) return rc;
+    CU(ctx->buf[B_CODES].ensure((total_steps + 8) * (c16 ? 2 : 1)));
+    GenParams G;
+    G.total_steps = total_steps;
+    G.chunk_steps = chunk;
+    G.cols = cols;
+    G.mrow = make_mod_const(rows);
+    G.mcol = make_mod_const(cols);
+    G.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
+    G.codes = ctx->buf[B_CODES].p;
+    G.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
+    if (total_steps == 0) return PCU_OK; /* engine untouched */
+    if (c16)
+        k_gen_codes<uint16_t><<<(unsigned)ctas, GEN_THREADS, 0, ctx->stream>>>(G);
+    else
+        k_gen_codes<uint8_t><<<(unsigned)ctas, GEN_THREADS, 0, ctx->stream>>>(G);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return fetch_end_window(ctx);
+}
+
+/* Exclusive prefix sum of per-rollout depths -> first step of each rollout. */
+__global__ void k_scan_block_sums(const uint16_t *depth, uint64_t n, uint64_t *block_sums) {
+    __shared__ unsigned long long sh[32];
+    const uint64_t i0 = (uint64_t)blockIdx.x * 4096;
+    unsigned long long s = 0;
+    for (uint32_t k = threadIdx.x; k < 4096; k += blockDim.x)
+        if (i0 + k < n) s += depth[i0 + k];
+    s = warp_sum_u64(s);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        unsigned long long v = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0;
+        v = warp_sum_u64(v);
+        if (threadIdx.x == 0) block_sums[blockIdx.x] = v;
+    }
+}
+__global__ void k_scan_finish(const uint16_t *depth, uint64_t n, const uint64_t *block_off, uint64_t *off) {
+    /* one warp per 4096-element block: sequential over 128 chunks of 32 */
+    const uint64_t i0 = (uint64_t)blockIdx.x * 4096;
+    const int lane = threadIdx.x;
+    unsigned long long run = block_off[blockIdx.x];
+    for (uint32_t k = 0; k < 4096; k += 32) {
+        const uint64_t i = i0 + k + lane;
+        unsigned long long v = (i < n) ? depth[i] : 0;
+        unsigned long long inc = v;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            unsigned long long y = __shfl_up_sync(PCU_FULL, inc, o);
+            if (lane >= o) inc += y;
+        }
+        if (i < n) off[i] = run + inc - v;
+        run += __shfl_sync(PCU_FULL, inc, 31);
+    }
+}
+
+int scan_depths(pcu_ctx *ctx, const uint16_t *d_depth, uint64_t n, const uint64_t **d_off, uint64_t *total) {
+    const uint64_t blocks = (n + 4095) / 4096;
+    CU(ctx->buf[B_STEPOFF].ensure(sizeof(uint64_t) * (n + 1)));
+    CU(ctx->buf[B_SCRATCH].ensure(sizeof(uint64_t) * (blocks + 1)));
+    uint64_t *off = reinterpret_cast<uint64_t *>(ctx->buf[B_STEPOFF].p);
+    uint64_t *bs = reinterpret_cast<uint64_t *>(ctx->buf[B_SCRATCH].p);
+    k_scan_block_sums<<<(unsigned)blocks, 256, 0, ctx->stream>>>(d_depth, n, bs);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    std::vector<uint64_t> h(blocks + 1);
+    CU(cudaMemcpyAsync(h.data(), bs, sizeof(uint64_t) * blocks, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    uint64_t acc = 0;
+    for (uint64_t b = 0; b < blocks; ++b) {
+        const uint64_t v = h[b];
+        h[b] = acc;
+        acc += v;
+    }
+    *total = acc;
+    CU(cudaMemcpyAsync(bs, h.data(), sizeof(uint64_t) * blocks, cudaMemcpyHostToDevice, ctx->stream));
+    k_scan_finish<<<(unsigned)blocks, 32, 0, ctx->stream>>>(d_depth, n, bs, off);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream));
+    *d_off = off;
+    return PCU_OK;
+}
+
+template <int KIND, int MODE>
+int launch_warp(pcu_ctx *ctx, const WarpParams &P) {
+    constexpr int ENGINES = (KIND == KIND_TREE ? 1 : 0) + (MODE == 1 ? 1 : 0);
+    const int warps = 8;
+    const size_t smem = (size_t)warps * MT_N * 4 * (ENGINES ? ENGINES : 1);
+    uint64_t blocks = (P.n + warps - 1) / warps;
+    const uint64_t cap = (uint64_t)ctx->sms * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks == 0) blocks = 1;
+    auto kern = k_warp<KIND, MODE>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)blocks, warps * 32, smem, ctx->stream>>>(P);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
+
+int check_common(pcu_ctx *ctx, const void *batch, const pcu_model_rng *rng, const pcu_out *out) {
+    if (!ctx) return PCU_ERR_INVALID;
+    if (!batch || !rng || !out) return fail(ctx, PCU_ERR_INVALID, "null batch, rng or out");
+    if (rng->mode == PCU_MODEL_STREAM) {
+        if (!rng->mt_x || !rng->mt_p) return fail(ctx, PCU_ERR_INVALID, "mode S needs mt_x and mt_p");
+        if (*rng->mt_p > MT_N) return fail(ctx, PCU_ERR_INVALID, "mt_p %u out of range", *rng->mt_p);
+    } else if (rng->mode == PCU_MODEL_PER_ROLLOUT) {
+        if (!rng->seeds) return fail(ctx, PCU_ERR_INVALID, "mode P needs seeds");
+    } else {
+        return fail(ctx, PCU_ERR_INVALID, "unknown model rng mode %d", rng->mode);
+    }
+    if (out->mem != PCU_MEM_HOST && out->mem != PCU_MEM_DEVICE) return fail(ctx, PCU_ERR_INVALID, "bad out->mem");
+    return PCU_OK;
+}
+
+int upload_fq(pcu_ctx *ctx, uint32_t T, const double **d_fq, uint32_t *fq_w) {
+    if (ctx->fq_w != 10 * T + 1) {
+        std::vector<double> fq;
+        uint32_t w;
+        host_build_fq(T, fq, &w);
+        CU(ctx->buf[B_FQ].ensure(sizeof(double) * fq.size()));
+        CU(cudaMemcpyAsync(ctx->buf[B_FQ].p, fq.data(), sizeof(double) * fq.size(), cudaMemcpyHostToDevice,
+                           ctx->stream));
+        CU(cudaStreamSynchronize(ctx->stream));
+        ctx->fq_w = w;
+    }
+    *d_fq = reinterpret_cast<const double *>(ctx->buf[B_FQ].p);
+    *fq_w = ctx->fq_w;
+    return PCU_OK;
+}
+
+}  // namespace
+
+/* =============================================================== C ABI ===== */
+
+extern "C" {
+
+int pcu_version(void) { return PCU_VERSION; }
+
+int pcu_create(int device_id, pcu_ctx **out) {
+    if (!out) return PCU_ERR_INVALID;
+    *out = nullptr;
+    int count = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess || device_id < 0 || device_id >= count) return PCU_ERR_CUDA;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device_id) != cudaSuccess) return PCU_ERR_CUDA;
+    if (prop.major != 10) return PCU_ERR_CUDA; /* sm_100a code only */
+    if (cudaSetDevice(device_id) != cudaSuccess) return PCU_ERR_CUDA;
+    pcu_ctx *ctx = new pcu_ctx();
+    ctx->device = device_id;
+    ctx->sms = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaMallocHost(reinterpret_cast<void **>(&ctx->pin_small), 4096 * sizeof(uint32_t)) != cudaSuccess) {
+        delete ctx;
+        return PCU_ERR_CUDA;
+    }
+    ctx->stream = ctx->own_stream;
+    *out = ctx;
+    return PCU_OK;
+}
+
+void pcu_destroy(pcu_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    for (auto &b : ctx->buf) b.release();
+    ctx->jump.release();
+    if (ctx->pin_small) cudaFreeHost(ctx->pin_small);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+}
+
+const char *pcu_last_error(const pcu_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+const char *pcu_last_path(const pcu_ctx *ctx) { return ctx ? ctx->path.c_str() : ""; }
+uint64_t pcu_kernel_launches(const pcu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return PCU_ERR_INVALID;
+    ctx->stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+    return PCU_OK;
+}
+
+int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
+    if (!ctx || !key) return PCU_ERR_INVALID;
+    if (!strcmp(key, "ctas_per_sm")) {
+        if (value < 1 || value > 8) return fail(ctx, PCU_ERR_INVALID, "ctas_per_sm must be 1..8");
+        ctx->ctas_per_sm = (int)value;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "force_general")) {
+        ctx->force_general = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "host_checkpoints")) {
+        ctx->host_checkpoints = value != 0;
+        return PCU_OK;
+    }
+    return fail(ctx, PCU_ERR_INVALID, "unknown option %s", key);
+}
+
+void *pcu_host_alloc(pcu_ctx *ctx, size_t bytes) {
+    if (!ctx) return nullptr;
+    void *p = nullptr;
+    cudaSetDevice(ctx->device);
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    return p;
+}
+void pcu_host_free(pcu_ctx *ctx, void *p) {
+    (void)ctx;
+    if (p) cudaFreeHost(p);
+}
+
+void pcu_mt_seed(uint64_t seed, uint32_t *mt_x, uint32_t *mt_p) { host_mt_seed(seed, mt_x, mt_p); }
+
+uint32_t pcu_mt_next(uint32_t *mt_x, uint32_t *mt_p) {
+    if (*mt_p >= MT_N) {
+        host_mt_refill(mt_x);
+        *mt_p = 0;
+    }
+    return mt_temper(mt_x[(*mt_p)++]);
+}
+
+int pcu_mt_discard(uint32_t *mt_x, uint32_t *mt_p, uint64_t n) {
+    if (!mt_x || !mt_p || *mt_p > MT_N) return PCU_ERR_INVALID;
+    if (n < (1ull << 22)) {
+        while (n) {
+            if (*mt_p >= MT_N) {
+                host_mt_refill(mt_x);
+                *mt_p = 0;
+            }
+            uint64_t take = MT_N - *mt_p;
+            if (take > n) take = n;
+            *mt_p += (uint32_t)take;
+            n -= take;
+        }
+        return PCU_OK;
+    }
+    uint32_t win[MT_N];
+    host_window_from_engine(mt_x, *mt_p, win);
+    if (!mt_jump_host(win, n)) return PCU_ERR_NOMEM;
+    engine_from_window(win, mt_x, mt_p);
+    return PCU_OK;
+}
+
+int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
+    int rc = check_common(ctx, b, rng, out);
+    if (rc) return rc;
+    ctx->err.clear();
+    if (b->mem != PCU_MEM_HOST && b->mem != PCU_MEM_DEVICE) return fail(ctx, PCU_ERR_INVALID, "bad batch->mem");
+    if (b->mem != out->mem) return fail(ctx, PCU_ERR_INVALID, "batch and out must share a memory space");
+    if (b->rows < 1 || b->cols < 1 || b->rows > 255 || b->cols > 255)
+        return fail(ctx, PCU_ERR_INVALID, "rows/cols must be 1..255");
+    if (b->transitions < 1 || b->transitions > 9)
+        return fail(ctx, PCU_ERR_INVALID, "transitions must be 1..9 (Rational<int> overflows beyond, SURVEY App. C6)");
+    if (b->thr_q <= 0 || b->thr_p < 0) return fail(ctx, PCU_ERR_INVALID, "chance_threshold must be p/q with p >= 0, q > 0");
+    if (!b->depth && b->depth_u == 0)
+        return fail(ctx, PCU_ERR_INVALID, "depth_bound 0 never terminates in the reference (random-tree.hh:95-99)");
+    const uint64_t n = b->n;
+    const uint32_t T = b->transitions;
+    const uint32_t gen_words = 2 * b->rows * b->cols * T;
+    if (!b->state_pos && b->state_pos_u < gen_words)
+        return fail(ctx, PCU_ERR_INVALID, "state_pos %u < 2*rows*cols*transitions = %u", b->state_pos_u, gen_words);
+    if (out->traj && out->traj_stride < (b->depth ? 1u : b->depth_u))
+        return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
+    CU(cudaSetDevice(ctx->device));
+    OutDev od;
+    if ((rc = prepare_out(ctx, out, n, od))) return rc;
+    if (n == 0) return finish_all(ctx, out, n, od, rng);
+
+    const uint32_t *d_pos;
+    const int32_t *d_bias;
+    const uint64_t *d_sseed, *d_tseed, *d_mseed = nullptr;
+    const uint16_t *d_depth;
+    if ((rc = stage_in(ctx, b->mem, b->state_pos, n, B_STATE_POS, &d_pos))) return rc;
+    if ((rc = stage_in(ctx, b->mem, b->payoff_bias, n, B_BIAS, &d_bias))) return rc;
+    if ((rc = stage_in(ctx, b->mem, b->state_seed, n, B_STATE_SEED, &d_sseed))) return rc;
+    if ((rc = stage_in(ctx, b->mem, b->transition_seed, n, B_TSEED, &d_tseed))) return rc;
+    if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
+    if (rng->mode == PCU_MODEL_PER_ROLLOUT)
+        if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+
+    const double *d_fq = nullptr;
+    uint32_t fq_w = 0;
+    if (T > 1 && (rc = upload_fq(ctx, T, &d_fq, &fq_w))) return rc;
+
+    /* ---- fused path: mode S, uniform depth, one shared state stream, host-visible positions */
+    bool fused = !ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && !b->state_seed &&
+                 (T == 1 || !b->transition_seed) && (!b->state_pos || b->mem == PCU_MEM_HOST);
+    uint32_t pos_min = b->state_pos_u, pos_max = b->state_pos_u;
+    if (fused && b->state_pos) {
+        pos_min = 0xffffffffu;
+        pos_max = 0;
+        for (uint64_t i = 0; i < n; ++i) {
+            pos_min = std::min(pos_min, b->state_pos[i]);
+            pos_max = std::max(pos_max, b->state_pos[i]);
+        }
+        if (pos_min < gen_words) return fail(ctx, PCU_ERR_INVALID, "a state_pos is below 2*rows*cols*transitions");
+    }
+    uint64_t span = 0;
+    if (fused) {
+        const uint64_t per_step = (uint64_t)b->rows * b->cols * T + 2 + gen_words;
+        span = (uint64_t)(pos_max - pos_min) + gen_words + per_step * b->depth_u + 8;
+        if (span > (1u << 22)) fused = false;
+    }
+    if (fused) {
+        const uint32_t tab_base = pos_min - gen_words;
+        const uint32_t tab_len = (uint32_t)span;
+        if (!(ctx->tab_key.valid && ctx->tab_key.seed == (uint32_t)b->state_seed_u && ctx->tab_key.base == tab_base &&
+              ctx->tab_key.len >= tab_len)) {
+            std::vector<uint8_t> tab;
+            host_build_table(b->state_seed_u, tab_base, tab_len, tab);
+            CU(ctx->buf[B_TAB].ensure(tab_len));
+            CU(cudaMemcpyAsync(ctx->buf[B_TAB].p, tab.data(), tab_len, cudaMemcpyHostToDevice, ctx->stream));
+            CU(cudaStreamSynchronize(ctx->stream));
+            ctx->tab_key.valid = true;
+            ctx->tab_key.seed = (uint32_t)b->state_seed_u;
+            ctx->tab_key.base = tab_base;
+            ctx->tab_key.len = tab_len;
+        }
+        StreamParams P;
+        memset(&P, 0, sizeof(P));
+        P.n = n;
+        P.depth = b->depth_u;
+        P.cols = b->cols;
+        P.T = T;
+        P.gen_words = gen_words;
+        P.mrow = make_mod_const(b->rows);
+        P.mcol = make_mod_const(b->cols);
+        P.tab = reinterpret_cast<const uint8_t *>(ctx->buf[B_TAB].p);
+        P.tab_base = tab_base;
+        P.tab_len = tab_len;
+        P.state_pos = d_pos;
+        P.state_pos_u = b->state_pos_u;
+        P.bias = d_bias;
+        P.bias_u = b->payoff_bias_u;
+        P.pu = (T > 1) ? host_uniform_from_seed(b->transition_seed_u) : 0.0;
+        P.thr_p = b->thr_p;
+        P.thr_q = b->thr_q;
+        P.fq = d_fq;
+        P.fq_w = fq_w;
+        P.traj_stride = out->traj_stride;
+        ctx->path = "stream_table";
+        if ((rc = run_stream<KIND_TREE>(ctx, P, b->rows, rng, od))) return rc;
+        return finish_all(ctx, out, n, od, rng);
+    }
+
+    /* ---- general path: one rollout per warp, private state engines */
+    WarpParams W;
+    memset(&W, 0, sizeof(W));
+    W.n = n;
+    W.rows = b->rows;
+    W.cols = b->cols;
+    W.T = T;
+    W.gen_words = gen_words;
+    W.mrow = make_mod_const(b->rows);
+    W.mcol = make_mod_const(b->cols);
+    W.state_seed = d_sseed;
+    W.state_seed_u = b->state_seed_u;
+    W.state_pos = d_pos;
+    W.state_pos_u = b->state_pos_u;
+    W.tseed = d_tseed;
+    W.tseed_u = b->transition_seed_u;
+    W.depth = d_depth;
+    W.depth_u = b->depth_u;
+    W.bias = d_bias;
+    W.bias_u = b->payoff_bias_u;
+    W.thr_p = b->thr_p;
+    W.thr_q = b->thr_q;
+    W.fq = d_fq;
+    W.fq_w = fq_w;
+    W.payoff = od.payoff;
+    W.traj = od.traj;
+    W.traj_stride = out->traj_stride;
+    W.traj_hash = od.hash;
+    W.sums = od.sums;
+    if (rng->mode == PCU_MODEL_STREAM) {
+        uint64_t total_steps = n * (uint64_t)b->depth_u;
+        if (d_depth) {
+            if ((rc = scan_depths(ctx, d_depth, n, &W.step_off, &total_steps))) return rc;
+        }
+        bool c16;
+        if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16))) return rc;
+        W.codes = ctx->buf[B_CODES].p;
+        W.code_u16 = c16;
+        ctx->path = "warp_private_S";
+        if ((rc = launch_warp<KIND_TREE, 0>(ctx, W))) return rc;
+    } else {
+        W.model_seeds = d_mseed;
+        ctx->path = "warp_private_P";
+        if ((rc = launch_warp<KIND_TREE, 1>(ctx, W))) return rc;
+    }
+    return finish_all(ctx, out, n, od, rng);
+}
+
+int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_out *out) {
+    int rc = check_common(ctx, b, rng, out);
+    if (rc) return rc;
+    ctx->err.clear();
+    if (b->mem != PCU_MEM_HOST && b->mem != PCU_MEM_DEVICE) return fail(ctx, PCU_ERR_INVALID, "bad batch->mem");
+    if (b->mem != out->mem) return fail(ctx, PCU_ERR_INVALID, "batch and out must share a memory space");
+    if (b->n_actions < 1 || b->n_actions > 255) return fail(ctx, PCU_ERR_INVALID, "n_actions must be 1..255");
+    if (out->traj && out->traj_stride < (b->depth ? 1u : b->depth_u))
+        return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
+    const uint64_t n = b->n;
+    CU(cudaSetDevice(ctx->device));
+    OutDev od;
+    if ((rc = prepare_out(ctx, out, n, od))) return rc;
+    if (n == 0) return finish_all(ctx, out, n, od, rng);
+    const uint16_t *d_depth;
+    const uint64_t *d_mseed = nullptr;
+    if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
+    if (rng->mode == PCU_MODEL_PER_ROLLOUT)
+        if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+
+    if (!ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && b->depth_u > 0) {
+        StreamParams P;
+        memset(&P, 0, sizeof(P));
+        P.n = n;
+        P.depth = b->depth_u;
+        P.cols = b->n_actions;
+        P.T = 1;
+        P.mrow = make_mod_const(b->n_actions);
+        P.mcol = make_mod_const(b->n_actions);
+        P.traj_stride = out->traj_stride;
+        ctx->path = "stream_mold";
+        if ((rc = run_stream<KIND_MOLD>(ctx, P, b->n_actions, rng, od))) return rc;
+        return finish_all(ctx, out, n, od, rng);
+    }
+    WarpParams W;
+    memset(&W, 0, sizeof(W));
+    W.n = n;
+    W.rows = b->n_actions;
+    W.cols = b->n_actions;
+    W.T = 1;
+    W.mrow = make_mod_const(b->n_actions);
+    W.mcol = make_mod_const(b->n_actions);
+    W.depth = d_depth;
+    W.depth_u = b->depth_u;
+    W.payoff = od.payoff;
+    W.traj = od.traj;
+    W.traj_stride = out->traj_stride;
+    W.traj_hash = od.hash;
+    W.sums = od.sums;
+    if (rng->mode == PCU_MODEL_STREAM) {
+        uint64_t total_steps = n * (uint64_t)b->depth_u;
+        if (d_depth) {
+            if ((rc = scan_depths(ctx, d_depth, n, &W.step_off, &total_steps))) return rc;
+        }
+        bool c16;
+        if ((rc = gen_codes(ctx, total_steps, b->n_actions, b->n_actions, rng, &c16))) return rc;
+        W.codes = ctx->buf[B_CODES].p;
+        W.code_u16 = c16;
+        ctx->path = "warp_mold_S";
+        if ((rc = launch_warp<KIND_MOLD, 0>(ctx, W))) return rc;
+    } else {
+        W.model_seeds = d_mseed;
+        ctx->path = "warp_mold_P";
+        if ((rc = launch_warp<KIND_MOLD, 1>(ctx, W))) return rc;
+    }
+    return finish_all(ctx, out, n, od, rng);
+}
+
+int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_second) {
+    if (!ctx || !ops_per_second) return PCU_ERR_INVALID;
+    CU(cudaSetDevice(ctx->device));
+    const int iters = 4096;
+    const int blocks = ctx->sms * 8, threads = 256;
+    CU(ctx->buf[B_SCRATCH].ensure(sizeof(uint32_t) * blocks * threads));
+    uint32_t *d = reinterpret_cast<uint32_t *>(ctx->buf[B_SCRATCH].p);
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    double best = 0;
+    for (int r = 0; r < reps + 1; ++r) {
+        CU(cudaEventRecord(e0, ctx->stream));
+        if (variant == 0)
+            k_int_peak<0><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters);
+        else if (variant == 1)
+            k_int_peak<1><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters);
+        else
+            k_int_peak<2><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters);
+        ctx->launches++;
+        CU(cudaEventRecord(e1, ctx->stream));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        const double ops = (double)blocks * threads * iters * INT_PEAK_OPS_PER_ITER;
+        if (r > 0 && ms > 0) best = std::max(best, ops / (ms * 1e-3));
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ops_per_second = best;
+    return PCU_OK;
+}
+
+}  // extern "C"

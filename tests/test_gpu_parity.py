@@ -1,0 +1,273 @@
+"""GPU parity: libpinyon_cuda (through its C ABI) against the oracle on the same seeded
+inputs — payoffs, (row, col, chance) trajectories, trajectory hashes, exact win/draw/loss
+sums and the post-batch model engine, all bit-exact."""
+import numpy as np
+import pytest
+
+from oracle import loader
+from pinyon_b200 import Engine, PcuError
+
+pytestmark = pytest.mark.gpu
+
+
+def run_tree(ctx, n, *, rows, cols, T=1, thr=(0, 1), depth, state_seed=0, pre=0, tseed=0, bias=0, engine=None,
+             model_seeds=None, want_traj=True):
+    gen = 2 * rows * cols * T
+    pos = (pre + gen) if np.isscalar(pre) else (pre.astype(np.uint32) + np.uint32(gen))
+    dmax = int(depth) if np.isscalar(depth) else int(depth.max())
+    out = dict(payoff=np.full(n, 255, np.uint8), traj_hash=np.zeros(n, np.uint32), sums=np.zeros(8, np.uint64))
+    out["traj"] = np.full((n, max(dmax, 1), 3), 255, np.uint8) if want_traj else None
+    d = depth if np.isscalar(depth) else depth.astype(np.uint16)
+    ctx.rollout_random_tree(n, rows=rows, cols=cols, transitions=T, thr=thr, depth=d, state_seed=state_seed,
+                            state_pos=pos, transition_seed=tseed, payoff_bias=bias, engine=engine,
+                            model_seeds=model_seeds, payoff=out["payoff"], traj=out["traj"], traj_stride=max(dmax, 1),
+                            traj_hash=out["traj_hash"], sums=out["sums"])
+    return out
+
+
+def check_same(got, exp, n):
+    assert np.array_equal(got["payoff"], exp["payoff"])
+    if got.get("traj") is not None:
+        assert np.array_equal(got["traj"], exp["traj"])
+    assert np.array_equal(got["traj_hash"], exp["traj_hash"])
+    assert np.array_equal(got["sums"], exp["sums"])
+    assert int(got["sums"][:3].sum()) == n
+
+
+def engine_matches(engine, seed, discarded, oracle):
+    exp = np.zeros(700, np.uint32)
+    oracle.orc_mt_words(seed, discarded, 700, exp.ctypes.data)
+    got = np.array([engine.next() for _ in range(700)], np.uint32)
+    return np.array_equal(got, exp)
+
+
+CASES = [
+    # rows, cols, T, thr, depth, state_seed, pre, tseed, bias, model_seed, model_pre
+    (3, 3, 1, (0, 1), 10, 0, 0, 0, 0, 0, 0),  # BASELINE config 1/2
+    (9, 9, 3, (0, 1), 20, 0, 0, 0, 0, 0, 0),  # BASELINE config 3
+    (2, 2, 2, (1, 2), 5, 7, 13, 1, 1, 99, 7),
+    (4, 7, 4, (3, 10), 9, 12345678901234, 700, 0xDEADBEEFCAFE, -2, 2**32 + 5, 1001),
+    (1, 1, 1, (0, 1), 1, 5, 0, 0, 0, 1, 623),
+    (5, 2, 9, (1, 1), 3, 99, 0, 3, 0, 3, 624),
+    (16, 17, 1, (0, 1), 6, 3, 0, 0, 0, 3, 2),  # rows*cols > 256 -> 16-bit action codes
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("n", [1, 223, 1000])
+def test_tree_shared_root_stream(ctx, oracle, case, n):
+    rows, cols, T, thr, depth, sseed, pre, tseed, bias, mseed, mpre = case
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth,
+                                      state_seed=sseed, state_pre_discard=pre, transition_seed=tseed, payoff_bias=bias,
+                                      model_seed=mseed, model_pre_discard=mpre)
+    eng = Engine(mseed).discard(mpre)
+    got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
+                   bias=bias, engine=eng)
+    assert ctx.last_path == "stream_table"
+    check_same(got, exp, n)
+    assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
+
+
+def test_tree_known_answers_appendix_b(ctx):
+    """vectors produced by the reference's own MonteCarloModel."""
+    b1 = [1, 0, 1, .5, 0, 1, 0, 1, 0, 1, 1, 1, 0, 1, .5, 1, 0, .5, 1, .5, 1, 1, 1, 1, 1, 1, .5, .5, 0, 1, 0, 0]
+    got = run_tree(ctx, 32, rows=3, cols=3, depth=10, engine=Engine(0))
+    assert (got["payoff"] / 2.0).tolist() == b1
+    assert got["traj"][0].tolist() == [[2, 2, 0], [1, 2, 0], [1, 1, 0], [0, 0, 0], [0, 2, 0], [1, 1, 0], [1, 0, 0],
+                                       [0, 1, 0], [2, 1, 0], [0, 0, 0]]
+    b2 = [0, 1, .5, .5, 1, 0, .5, 1, 1, 1, 0, 0, 0, 0, .5, 0, 1, 0, 0, 1, 1, 1, 1, 1, 1, .5, 0, 1, 0, 1, 0, 0]
+    got = run_tree(ctx, 32, rows=9, cols=9, T=3, depth=20, engine=Engine(0))
+    assert (got["payoff"] / 2.0).tolist() == b2
+    assert got["traj"][0][:4].tolist() == [[5, 5, 1], [7, 2, 1], [4, 7, 0], [0, 6, 1]]
+    # 10^6 rollouts of B1: wins 364521, draws 159742, losses 475737
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_random_tree(10**6, rows=3, cols=3, depth=10, engine=Engine(0), sums=sums)
+    assert sums[:4].tolist() == [364521, 159742, 475737, 10**7]
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_random_tree(20000, rows=9, cols=9, transitions=3, depth=20, engine=Engine(0), sums=sums)
+    assert sums[:3].tolist() == [8949, 2124, 8927]
+
+
+def test_tree_shared_root_ragged_positions(ctx, oracle):
+    """One state stream, per-rollout positions and biases (what search leaves look like)."""
+    rng = np.random.default_rng(3)
+    n = 777
+    pre = rng.integers(0, 400, n).astype(np.uint32)
+    bias = rng.integers(-3, 4, n).astype(np.int32)
+    for rows, cols, T, thr in [(3, 3, 1, (0, 1)), (4, 3, 3, (3, 10))]:
+        exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=8,
+                                          state_seed=11, state_pre_discard=pre, transition_seed=5, payoff_bias=bias,
+                                          model_seed=4)
+        eng = Engine(4)
+        got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=8, state_seed=11, pre=pre, tseed=5, bias=bias,
+                       engine=eng)
+        assert ctx.last_path == "stream_table"
+        check_same(got, exp, n)
+
+
+@pytest.mark.parametrize("mode", ["S", "P"])
+@pytest.mark.parametrize("shape", [(3, 3, 1, (0, 1)), (9, 9, 3, (0, 1)), (5, 4, 3, (3, 10)), (2, 6, 2, (1, 2))])
+def test_tree_private_roots(ctx, oracle, mode, shape):
+    """Distinct roots: private state engines, ragged depth, per-rollout transition seeds."""
+    rows, cols, T, thr = shape
+    rng = np.random.default_rng(rows * 100 + cols)
+    n = 500
+    kw = dict(state_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+              state_pre_discard=rng.integers(0, 1500, n).astype(np.uint32),
+              transition_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+              depth=rng.integers(1, 14, n).astype(np.uint32),
+              payoff_bias=rng.integers(-2, 3, n).astype(np.int32))
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64) if mode == "P" else None
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, model_seed=21,
+                                      model_pre_discard=5, model_seeds=mseeds, **kw)
+    eng = Engine(21).discard(5)
+    got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=kw["depth"], state_seed=kw["state_seed"],
+                   pre=kw["state_pre_discard"], tseed=kw["transition_seed"], bias=kw["payoff_bias"],
+                   engine=None if mode == "P" else eng, model_seeds=mseeds)
+    assert ctx.last_path == "warp_private_" + mode
+    check_same(got, exp, n)
+    if mode == "S":
+        assert engine_matches(eng, 21, 5 + 4 * int(kw["depth"].sum()), oracle)
+
+
+def test_tree_general_path_equals_fused(ctx, oracle):
+    """force_general routes a shared-root batch through the warp kernel: same answers."""
+    n = 600
+    exp = loader.random_tree_rollouts(oracle, n, rows=9, cols=9, transitions=3, depth=20, model_seed=0)
+    ctx.set_option("force_general", 1)
+    try:
+        got = run_tree(ctx, n, rows=9, cols=9, T=3, depth=20, engine=Engine(0))
+        assert ctx.last_path == "warp_private_S"
+    finally:
+        ctx.set_option("force_general", 0)
+    check_same(got, exp, n)
+
+
+@pytest.mark.parametrize("n_actions,depth", [(2, 10), (2, 50), (3, 1), (7, 4), (17, 3)])
+@pytest.mark.parametrize("n", [1, 500])
+def test_mold_stream(ctx, oracle, n_actions, depth, n):
+    exp = loader.mold_rollouts(oracle, n, n_actions=n_actions, depth=depth, model_seed=0, model_pre_discard=3)
+    eng = Engine(0).discard(3)
+    payoff = np.full(n, 255, np.uint8)
+    traj = np.full((n, depth, 3), 255, np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_mold(n, n_actions=n_actions, depth=depth, engine=eng, payoff=payoff, traj=traj, traj_stride=depth,
+                     traj_hash=th, sums=sums)
+    assert ctx.last_path == "stream_mold"
+    assert not payoff.any()  # MoldState never sets a payoff: (0, 0)
+    assert np.array_equal(traj, exp["traj"])
+    assert np.array_equal(th, exp["traj_hash"])
+    assert np.array_equal(sums, exp["sums"])
+    assert engine_matches(eng, 0, 3 + 4 * depth * n, oracle)
+
+
+@pytest.mark.parametrize("mode", ["S", "P"])
+def test_mold_ragged(ctx, oracle, mode):
+    rng = np.random.default_rng(8)
+    n = 400
+    depth = rng.integers(0, 30, n).astype(np.uint32)  # depth 0 is a terminal root: no steps
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64) if mode == "P" else None
+    exp = loader.mold_rollouts(oracle, n, n_actions=3, depth=depth, model_seed=6, model_seeds=mseeds)
+    eng = Engine(6)
+    traj = np.zeros((n, int(depth.max()), 3), np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_mold(n, n_actions=3, depth=depth.astype(np.uint16), engine=None if mode == "P" else eng,
+                     model_seeds=mseeds, traj=traj, traj_stride=int(depth.max()), traj_hash=th, sums=sums)
+    assert ctx.last_path == "warp_mold_" + mode
+    assert np.array_equal(traj, exp["traj"])
+    assert np.array_equal(th, exp["traj_hash"])
+    assert np.array_equal(sums, exp["sums"])
+
+
+def test_jump_ahead_checkpoints_match_host_stepping(ctx, oracle):
+    """Many CTAs, each starting mid-stream: the device jump-ahead against plain stepping on
+    the host, and both against the oracle."""
+    n = 224 * 1300 + 57  # > 592 rounds -> several rounds per CTA, hundreds of checkpoints
+    outs = []
+    for host in (1, 0):
+        ctx.set_option("host_checkpoints", host)
+        eng = Engine(0)
+        got = run_tree(ctx, n, rows=3, cols=3, depth=10, engine=eng, want_traj=False)
+        outs.append((got, [eng.next() for _ in range(8)]))
+    ctx.set_option("host_checkpoints", 0)
+    assert np.array_equal(outs[0][0]["payoff"], outs[1][0]["payoff"])
+    assert np.array_equal(outs[0][0]["traj_hash"], outs[1][0]["traj_hash"])
+    assert outs[0][1] == outs[1][1]
+    exp = loader.random_tree_rollouts(oracle, n, rows=3, cols=3, depth=10, want_traj=False)
+    check_same(outs[1][0], exp, n)
+
+
+def test_batch_continuation(ctx):
+    """Mode S is one stream: a batch run in two calls equals the same batch in one."""
+    n = 50000
+    eng = Engine(9)
+    whole = run_tree(ctx, n, rows=9, cols=9, T=3, depth=20, engine=eng, want_traj=False)
+    eng2 = Engine(9)
+    a = run_tree(ctx, 12345, rows=9, cols=9, T=3, depth=20, engine=eng2, want_traj=False)
+    b = run_tree(ctx, n - 12345, rows=9, cols=9, T=3, depth=20, engine=eng2, want_traj=False)
+    assert np.array_equal(np.concatenate([a["payoff"], b["payoff"]]), whole["payoff"])
+    assert np.array_equal(np.concatenate([a["traj_hash"], b["traj_hash"]]), whole["traj_hash"])
+    assert np.array_equal(a["sums"] + b["sums"], whole["sums"])
+    assert [eng.next() for _ in range(4)] == [eng2.next() for _ in range(4)]
+
+
+def test_device_resident_batch(ctx, oracle):
+    torch = pytest.importorskip("torch")
+    n = 3000
+    exp = loader.random_tree_rollouts(oracle, n, rows=9, cols=9, transitions=3, depth=20, want_traj=False)
+    payoff = torch.zeros(n, dtype=torch.uint8, device="cuda")
+    th = torch.zeros(n, dtype=torch.int32, device="cuda")
+    sums = torch.zeros(8, dtype=torch.int64, device="cuda")
+    ctx.rollout_random_tree(n, rows=9, cols=9, transitions=3, depth=20, engine=Engine(0), payoff=payoff, traj_hash=th,
+                            sums=sums)
+    torch.cuda.synchronize()
+    assert np.array_equal(payoff.cpu().numpy(), exp["payoff"])
+    assert np.array_equal(th.cpu().numpy().view(np.uint32), exp["traj_hash"])
+    assert np.array_equal(sums.cpu().numpy().view(np.uint64), exp["sums"])
+    # per-rollout device arrays go through the general path
+    seeds = torch.arange(n, dtype=torch.int64, device="cuda")
+    exp = loader.random_tree_rollouts(oracle, n, rows=3, cols=3, depth=10, state_seed=np.arange(n, dtype=np.uint64),
+                                      want_traj=False)
+    ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, state_seed=seeds, engine=Engine(0), payoff=payoff)
+    torch.cuda.synchronize()
+    assert np.array_equal(payoff.cpu().numpy(), exp["payoff"])
+
+
+def test_empty_and_invalid(ctx):
+    sums = np.ones(8, np.uint64)
+    eng = Engine(1)
+    before = eng.x.copy()
+    ctx.rollout_random_tree(0, rows=3, cols=3, depth=10, engine=eng, sums=sums)
+    assert not sums.any() and np.array_equal(eng.x, before)
+    for bad in (dict(rows=3, cols=3, depth=0), dict(rows=0, cols=3, depth=1), dict(rows=3, cols=3, depth=1, transitions=10),
+                dict(rows=3, cols=3, depth=2, state_pos=3)):
+        with pytest.raises(PcuError) as e:
+            ctx.rollout_random_tree(4, engine=Engine(0), **bad)
+        assert e.value.code == -1
+    with pytest.raises(PcuError):
+        ctx.rollout_mold(4, n_actions=0, depth=3, engine=Engine(0))
+
+
+def test_full_size_properties(ctx, oracle):
+    """BASELINE config 2 size (2^24 rollouts, 3x3x1, depth 10): exact counts, sampled windows
+    against the oracle, and the post-batch engine against the host jump-ahead."""
+    n = 1 << 24
+    eng = Engine(0)
+    payoff = np.zeros(n, np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, engine=eng, payoff=payoff, traj_hash=th, sums=sums)
+    assert int(sums[:3].sum()) == n and int(sums[3]) == 10 * n
+    counts = np.bincount(payoff, minlength=3)
+    assert counts.tolist() == [int(sums[2]), int(sums[1]), int(sums[0])]
+    assert int(th.astype(np.uint64).sum()) == int(sums[4])
+    assert payoff[:10**6].tolist().count(2) == 364521  # Appendix B1 prefix
+    for start in (0, 5_000_000, n - 4096):
+        exp = loader.random_tree_rollouts(oracle, 4096, rows=3, cols=3, depth=10, model_pre_discard=40 * start,
+                                          want_traj=False)
+        assert np.array_equal(payoff[start:start + 4096], exp["payoff"])
+        assert np.array_equal(th[start:start + 4096], exp["traj_hash"])
+    ref = Engine(0).discard(40 * n)
+    assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
