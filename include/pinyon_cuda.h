@@ -57,6 +57,9 @@ int pcu_version(void);
 int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream);
 /* Number of kernels launched by this context since creation (bench.py gpu_launches). */
 uint64_t pcu_kernel_launches(const pcu_ctx *ctx);
+/* Device time in ms of the rollout kernel (k_stream / k_warp) of the last rollout call,
+ * from CUDA events recorded on the launching stream around that launch; -1 if none. */
+double pcu_last_kernel_ms(pcu_ctx *ctx);
 /* Tuning knobs, mainly for benchmarks: key "ctas_per_sm" (1..8) sets the number of
  * model-stream chunks per SM of the fused stream kernels.  Returns PCU_ERR_INVALID
  * for unknown keys. */

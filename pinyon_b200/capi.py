@@ -29,7 +29,7 @@ HASH_MUL = 16777619
 
 # every symbol include/pinyon_cuda.h declares
 EXPORTS = [
-    "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches",
+    "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches", "pcu_last_kernel_ms",
     "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
 ]
@@ -94,6 +94,8 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_set_stream.argtypes = [vp, vp]
     lib.pcu_kernel_launches.argtypes = [vp]
     lib.pcu_kernel_launches.restype = u64
+    lib.pcu_last_kernel_ms.argtypes = [vp]
+    lib.pcu_last_kernel_ms.restype = C.c_double
     lib.pcu_set_option.argtypes = [vp, C.c_char_p, C.c_int64]
     lib.pcu_host_alloc.argtypes = [vp, C.c_size_t]
     lib.pcu_host_alloc.restype = vp
@@ -194,6 +196,10 @@ class Context:
     @property
     def launches(self) -> int:
         return self.lib.pcu_kernel_launches(self.h)
+
+    @property
+    def last_kernel_ms(self) -> float:
+        return self.lib.pcu_last_kernel_ms(self.h)
 
     @property
     def last_path(self) -> str:

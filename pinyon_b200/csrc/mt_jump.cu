@@ -312,8 +312,8 @@ int MtJump::run(cudaStream_t stream, const uint32_t *base_window, uint64_t count
     }
     int levels = 0;
     while ((1ull << levels) < count) ++levels;
-    const uint64_t max_src = std::min<uint64_t>(1ull << (levels - 1), count - (1ull << (levels - 1)));
-    const uint64_t need_src = std::max<uint64_t>(max_src, 1);
+    uint64_t need_src = 1; /* the widest level of the doubling tree */
+    for (int k = 0; k < levels; ++k) need_src = std::max<uint64_t>(need_src, std::min<uint64_t>(1ull << k, count - (1ull << k)));
     if (ext_cap < need_src) {
         if (d_ext) cudaFree(d_ext);
         d_ext = nullptr;

@@ -50,6 +50,8 @@ struct pcu_ctx {
     int sms = 0;
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr; /* bracket the rollout kernel of the last call */
+    bool ev_valid = false;
     std::string err;
     std::string path;
     uint64_t launches = 0;
@@ -343,7 +345,10 @@ template <int KIND, typename CodeT>
 int launch_stream(pcu_ctx *ctx, const StreamParams &P, uint64_t ctas, bool tab_smem, size_t smem) {
     auto kern = tab_smem ? k_stream<KIND, CodeT, true> : k_stream<KIND, CodeT, false>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
     kern<<<(unsigned)ctas, GEN_THREADS, smem, ctx->stream>>>(P);
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
     ctx->launches++;
     CU(cudaGetLastError());
     return PCU_OK;
@@ -490,7 +495,10 @@ int launch_warp(pcu_ctx *ctx, const WarpParams &P) {
     if (blocks == 0) blocks = 1;
     auto kern = k_warp<KIND, MODE>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
     kern<<<(unsigned)blocks, warps * 32, smem, ctx->stream>>>(P);
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
     ctx->launches++;
     CU(cudaGetLastError());
     return PCU_OK;
@@ -553,6 +561,10 @@ int pcu_create(int device_id, pcu_ctx **out) {
         return PCU_ERR_CUDA;
     }
     ctx->stream = ctx->own_stream;
+    if (cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+        delete ctx;
+        return PCU_ERR_CUDA;
+    }
     *out = ctx;
     return PCU_OK;
 }
@@ -564,6 +576,8 @@ void pcu_destroy(pcu_ctx *ctx) {
     for (auto &b : ctx->buf) b.release();
     ctx->jump.release();
     if (ctx->pin_small) cudaFreeHost(ctx->pin_small);
+    if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+    if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -571,6 +585,14 @@ void pcu_destroy(pcu_ctx *ctx) {
 const char *pcu_last_error(const pcu_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 const char *pcu_last_path(const pcu_ctx *ctx) { return ctx ? ctx->path.c_str() : ""; }
 uint64_t pcu_kernel_launches(const pcu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+double pcu_last_kernel_ms(pcu_ctx *ctx) {
+    if (!ctx || !ctx->ev_valid) return -1.0;
+    float ms = 0;
+    if (cudaEventSynchronize(ctx->ev1) != cudaSuccess || cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) != cudaSuccess)
+        return -1.0;
+    return (double)ms;
+}
 
 int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream) {
     if (!ctx) return PCU_ERR_INVALID;
