@@ -1,0 +1,46 @@
+"""Build tests/cpp/_bin/test_dropin: the C++23 drop-in test of PinyonCuda::MonteCarloModel.
+
+Needs the reference headers (present in the build container only); the binary is git-ignored
+and travels to the GPU box with the snapshot, like libpinyon_cuda.so.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+ROOT = HERE.parent.parent
+REFERENCE = Path(os.environ.get("PINYON_REFERENCE", "/root/reference"))
+BIN = HERE / "_bin" / "test_dropin"
+SOURCES = [HERE / "test_dropin.cc", *sorted((ROOT / "include" / "pinyon_cuda").glob("*.hh")), ROOT / "include" / "pinyon_cuda.h"]
+
+
+def reference_available() -> bool:
+    return (REFERENCE / "src" / "model" / "monte-carlo-model.hh").exists()
+
+
+def is_stale() -> bool:
+    if not BIN.exists():
+        return True
+    t = BIN.stat().st_mtime
+    return any(p.stat().st_mtime > t for p in SOURCES)
+
+
+def build(force: bool = False) -> Path:
+    if not reference_available():
+        raise RuntimeError(f"{REFERENCE} is not present: test_dropin can only be built next to the reference")
+    if not force and not is_stale():
+        return BIN
+    BIN.parent.mkdir(exist_ok=True)
+    cmd = ["g++", "-std=c++23", "-O2", "-pthread", "-I", str(ROOT / "oracle" / "shim"), "-I", str(REFERENCE / "src"),
+           "-I", str(ROOT / "include"), "-o", str(BIN), str(HERE / "test_dropin.cc"), "-L", str(ROOT / "pinyon_b200"),
+           "-lpinyon_cuda", "-Wl,-rpath,$ORIGIN/../../../pinyon_b200"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("g++ failed:\n" + res.stderr[-4000:])
+    return BIN
+
+
+if __name__ == "__main__":
+    print(build(force=True))

@@ -1,0 +1,362 @@
+// Drop-in test of PinyonCuda::MonteCarloModel against the reference's own MonteCarloModel.
+//
+// Compiled (tests/cpp/build.py) with g++ -std=c++23 against the UNMODIFIED reference headers
+// under /root/reference/src and linked to libpinyon_cuda.so.  The reference classes here are
+// the checker; the GPU model is the thing checked.  Reads like the reference's own tests
+// (tests/flat.cc, tests/cart/node.cc, benchmark/mold-state.cc): same type lists, same calls.
+//
+//   test_dropin --cpu   host logic only (engine access, stream locator, concepts, loud failure)
+//   test_dropin --gpu   everything, on cuda:0
+#include <array>
+#include <atomic>
+#include <chrono>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <thread>
+#include <unordered_map>
+#include <vector>
+
+#include <model/monte-carlo-model.hh>
+#include <state/random-tree.hh>
+#include <state/test-states.hh>
+
+#include <algorithm/tree-bandit/bandit/exp3.hh>
+#include <algorithm/tree-bandit/tree/off-policy.hh>
+#include <algorithm/tree-bandit/tree/tree-bandit.hh>
+#include <tree/tree.hh>
+
+#include <pinyon_cuda/monte_carlo_model.hh>
+
+using RefTree = MonteCarloModel<RandomTree<>>;
+using GpuTree = PinyonCuda::MonteCarloModel<RandomTree<>>;
+using RefMold = MonteCarloModel<MoldState<>>;
+using GpuMold = PinyonCuda::MonteCarloModel<MoldState<>>;
+using GpuTreePolicy = PinyonCuda::MonteCarloModel<RandomTree<>, true>;
+
+// ---- the concepts every caller constrains its model with (src/model/model.hh:8-79)
+static_assert(IsValueModelTypes<GpuTree>);
+static_assert(IsSingleModelTypes<GpuTree>);
+static_assert(IsBatchModelTypes<GpuTree>);
+static_assert(IsValueModelTypes<GpuMold>);
+static_assert(IsSingleModelTypes<GpuMold>);
+static_assert(IsBatchModelTypes<GpuMold>);
+static_assert(IsPolicyModelTypes<GpuTreePolicy>);
+static_assert(IsSingleModelTypes<GpuTreePolicy>);
+static_assert(std::is_copy_constructible_v<GpuTree::Model>);
+// ---- and the callers named in north_star instantiate over it
+static_assert(IsBanditAlgorithmTypes<Exp3<GpuTree>>);
+static_assert(IsSearchTypes<TreeBandit<Exp3<GpuTree>>>);
+static_assert(IsSearchTypes<TreeBandit<Exp3<GpuMold>>>);
+
+static int g_failures = 0;
+#define CHECK(cond)                                                          \
+    do {                                                                     \
+        if (!(cond)) {                                                       \
+            std::printf("FAIL %s:%d: %s\n", __FILE__, __LINE__, #cond);      \
+            ++g_failures;                                                    \
+        }                                                                    \
+    } while (0)
+
+// ------------------------------------------------------------------ host-only checks
+
+static void test_engine_access() {
+    for (uint64_t seed : {0ull, 7ull, 12345678901234ull}) {
+        for (size_t adv : {size_t(0), size_t(1), size_t(623), size_t(624), size_t(625), size_t(5000)}) {
+            prng a{seed};
+            a.discard(adv);
+            PinyonCuda::EngineImage fast, slow;
+            PinyonCuda::EngineAccess<prng>::read(a, fast);
+            PinyonCuda::detail::image_from_stream(PinyonCuda::detail::engine_of(a), slow);
+            CHECK(fast.x == slow.x && fast.p == slow.p);
+            // the C ABI's host engine continues the image exactly as the prng continues
+            PinyonCuda::EngineImage img = fast;
+            for (int i = 0; i < 1500; ++i) {
+                const uint64_t hi = pcu_mt_next(img.x.data(), &img.p), lo = pcu_mt_next(img.x.data(), &img.p);
+                CHECK(((hi << 32) | lo) == a.uniform_64());
+            }
+            // write-back puts a fresh prng in the same place
+            prng b{seed + 99};
+            PinyonCuda::EngineAccess<prng>::write(b, img);
+            for (int i = 0; i < 1500; ++i) CHECK(a.uniform_64() == b.uniform_64());
+        }
+    }
+    std::printf("engine access ok (libstdc++ peek: %d)\n", int(PinyonCuda::detail::GLIBCXX_PEEK));
+}
+
+static void test_stream_locator() {
+    PinyonCuda::StreamLocator loc;
+    for (uint64_t seed : {0ull, 3ull, (1ull << 32) + 5}) {
+        prng d{seed};
+        uint64_t drawn = 0;
+        prng walker{seed * 31 + 1};
+        for (int i = 0; i < 400; ++i) {
+            PinyonCuda::EngineImage img;
+            PinyonCuda::EngineAccess<prng>::read(d, img);
+            CHECK(loc.locate(seed, img) == drawn);
+            const size_t adv = walker.random_int(1500);
+            d.discard(adv);
+            drawn += adv;
+        }
+        PinyonCuda::EngineImage img;
+        PinyonCuda::EngineAccess<prng>::read(prng{seed + 1}, img);
+        prng other{seed + 1};
+        other.discard(10);
+        PinyonCuda::EngineAccess<prng>::read(other, img);
+        CHECK(loc.locate(seed, img) != 10 || seed + 1 == seed);
+    }
+    // a RandomTree root and its descendants: position == draws its device made
+    RandomTree<>::State s{prng{5}, 12, 4, 3, 2};
+    PinyonCuda::TreeImage t = PinyonCuda::serialise_tree(s, loc);
+    CHECK(t.state_pos == 2 * 4 * 3 * 2 && t.depth == 12 && t.payoff_bias == 0 && t.state_seed == 5);
+    uint64_t expect = t.state_pos;
+    for (int step = 0; step < 6; ++step) {
+        const int r = step % 4, c = (step * 2) % 3, ch = step % 2;
+        s.apply_actions(r, c, ch);
+        expect += (r * 3 * 2 + c * 2 + ch) + 2 + 2 * 4 * 3 * 2;
+        t = PinyonCuda::serialise_tree(s, loc);
+        CHECK(t.state_pos == expect && t.depth == 12 - step - 1);
+    }
+    std::printf("stream locator ok\n");
+}
+
+static void test_loud_failure_without_gpu() {
+    pcu_ctx *probe = nullptr;
+    if (pcu_create(0, &probe) == PCU_OK) { /* a GPU is present: nothing to fail about */
+        pcu_destroy(probe);
+        return;
+    }
+    bool threw = false;
+    try {
+        GpuTree::Model model{prng{0}};
+    } catch (const PinyonCuda::Error &e) {
+        threw = true;
+        std::printf("no GPU -> %s\n", e.what());
+    }
+    CHECK(threw);
+}
+
+// ------------------------------------------------------------------ GPU parity checks
+
+template <typename A, typename B>
+static bool same_value(const A &a, const B &b) {
+    return a.get_row_value() == b.get_row_value() && a.get_col_value() == b.get_col_value();
+}
+
+// Single-state inference in sequence on one model: values AND the model engine stay in lock-step.
+static void test_single_inference() {
+    struct Cfg { uint64_t seed; size_t depth, rows, cols, T; int thr_p, thr_q; uint64_t tseed; };
+    const Cfg cfgs[] = {{0, 10, 3, 3, 1, 0, 1, 0}, {0, 20, 9, 9, 3, 0, 1, 0}, {7, 6, 2, 5, 4, 3, 10, 0xdeadbeefcafeull},
+                        {(1ull << 32) + 5, 8, 4, 4, 2, 1, 2, 1}};
+    for (const Cfg &c : cfgs) {
+        RandomTree<>::State root{prng{c.seed}, c.depth, c.rows, c.cols, c.T, Rational<>{c.thr_p, c.thr_q}};
+        root.randomize_transition(c.tseed);
+        RefTree::Model ref{prng{11}};
+        GpuTree::Model gpu{prng{11}};
+        for (int i = 0; i < 40; ++i) {
+            RefTree::ModelOutput a;
+            GpuTree::ModelOutput b;
+            ref.inference(RandomTree<>::State{root}, a);
+            gpu.inference(RandomTree<>::State{root}, b);
+            CHECK(same_value(a.value, b.value));
+        }
+        CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+    }
+    {
+        RefMold::Model ref{prng{3}};
+        GpuMold::Model gpu{prng{3}};
+        for (int i = 0; i < 20; ++i) {
+            RefMold::ModelOutput a;
+            GpuMold::ModelOutput b;
+            ref.inference(MoldState<>::State{2, 10}, a);
+            gpu.inference(MoldState<>::State{2, 10}, b);
+            CHECK(same_value(a.value, b.value));
+        }
+        CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+    }
+    {   // has_policy = true: uniform policies (monte-carlo-model.hh:45-53)
+        GpuTreePolicy::Model gpu{prng{0}};
+        MonteCarloModel<RandomTree<>, true>::Model ref{prng{0}};
+        GpuTreePolicy::ModelOutput b;
+        MonteCarloModel<RandomTree<>, true>::ModelOutput a;
+        RandomTree<>::State root{prng{0}, 5, 3, 4, 1};
+        ref.inference(RandomTree<>::State{root}, a);
+        gpu.inference(RandomTree<>::State{root}, b);
+        CHECK(same_value(a.value, b.value));
+        CHECK(a.row_policy == b.row_policy && a.col_policy == b.col_policy && b.row_policy.size() == 3);
+    }
+    std::printf("single inference ok\n");
+}
+
+// Batched inference over mid-tree leaves (different positions, depths, biases; some terminal),
+// exactly the batches a search produces (off-policy.hh:131-147).
+static void test_batch_inference() {
+    struct Cfg { uint64_t seed; size_t depth, rows, cols, T; int thr_p, thr_q; };
+    const Cfg cfgs[] = {{0, 10, 3, 3, 1, 0, 1}, {0, 20, 9, 9, 3, 0, 1}, {99, 5, 4, 2, 3, 3, 10}};
+    for (const Cfg &c : cfgs) {
+        const RandomTree<>::State root{prng{c.seed}, c.depth, c.rows, c.cols, c.T, Rational<>{c.thr_p, c.thr_q}};
+        prng walker{c.seed + 17};
+        RefTree::Model ref{prng{5}};
+        GpuTree::Model gpu{prng{5}};
+        RefTree::ModelBatchInput ref_in{};
+        GpuTree::ModelBatchInput gpu_in{};
+        const int n = 1500;
+        for (int i = 0; i < n; ++i) {
+            RandomTree<>::State s{root};
+            if (i % 7 == 3) s.randomize_transition(walker);
+            const int down = walker.random_int(static_cast<int>(c.depth) + 1); /* == depth -> terminal */
+            for (int k = 0; k < down; ++k) {
+                s.apply_actions(walker.random_int(c.rows), walker.random_int(c.cols));
+                s.get_actions();
+            }
+            RandomTree<>::State s2{s};
+            ref.add_to_batch_input(std::move(s), ref_in);
+            gpu.add_to_batch_input(std::move(s2), gpu_in);
+        }
+        CHECK(gpu_in.size() == size_t(n));
+        RefTree::ModelBatchOutput ref_out{};
+        GpuTree::ModelBatchOutput gpu_out{};
+        ref.inference(ref_in, ref_out);
+        gpu.inference(gpu_in, gpu_out);
+        CHECK(gpu_out.size() == ref_out.size());
+        int bad = 0;
+        double mean = 0;
+        size_t live = 0;
+        for (int i = 0; i < n; ++i) {
+            RefTree::ModelOutput a;
+            GpuTree::ModelOutput b;
+            ref.get_output(a, ref_out, i);
+            gpu.get_output(b, gpu_out, i);
+            bad += !same_value(a.value, b.value);
+            if (gpu_out.slot[i] >= 0) {
+                mean += a.value.get_row_value();
+                ++live;
+            }
+        }
+        CHECK(bad == 0);
+        CHECK(live && gpu_out.mean_row_value() == mean / double(live)); /* exact: payoffs are 0, 1/2, 1 */
+        CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+    }
+    {   // MoldState batch, ragged depths
+        RefMold::Model ref{prng{8}};
+        GpuMold::Model gpu{prng{8}};
+        RefMold::ModelBatchInput ref_in{};
+        GpuMold::ModelBatchInput gpu_in{};
+        for (int i = 0; i < 700; ++i) {
+            MoldState<>::State s{3, size_t(i % 13)}; /* depth 0 is terminal at construction */
+            MoldState<>::State s2{s};
+            ref.add_to_batch_input(std::move(s), ref_in);
+            gpu.add_to_batch_input(std::move(s2), gpu_in);
+        }
+        RefMold::ModelBatchOutput ref_out{};
+        GpuMold::ModelBatchOutput gpu_out{};
+        ref.inference(ref_in, ref_out);
+        gpu.inference(gpu_in, gpu_out);
+        for (int i = 0; i < 700; ++i) {
+            RefMold::ModelOutput a;
+            GpuMold::ModelOutput b;
+            ref.get_output(a, ref_out, i);
+            gpu.get_output(b, gpu_out, i);
+            CHECK(same_value(a.value, b.value));
+        }
+        CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+    }
+    std::printf("batch inference ok\n");
+}
+
+// Unmodified callers over the GPU model: TreeBandit<Exp3> (tree-bandit.hh:79-164, single-leaf
+// inference) and OffPolicy<Exp3> (off-policy.hh:83-109, batched leaves) must build the same tree
+// as over the reference model — same seeds, same root statistics.
+template <typename Types>
+static std::vector<double> tree_bandit_root(size_t iterations) {
+    typename Types::PRNG device{0};
+    typename Types::State state{prng{0}, 10, 3, 3, 1};
+    typename Types::Model model{prng{0}};
+    typename Types::MatrixNode root{};
+    typename Types::Search search{};
+    search.run_for_iterations(iterations, device, state, model, root);
+    std::vector<double> s{double(root.count_matrix_nodes()), double(root.stats.visits),
+                          double(root.stats.value_total.get_row_value())};
+    for (auto v : root.stats.row_visits) s.push_back(v);
+    for (auto v : root.stats.col_visits) s.push_back(v);
+    return s;
+}
+
+template <typename Types>
+static std::vector<double> off_policy_root(size_t learner, size_t actor) {
+    typename Types::PRNG device{0};
+    std::vector<typename Types::State> states;
+    states.emplace_back(prng{0}, 10, 3, 3, 1);
+    typename Types::Model model{prng{0}};
+    std::vector<typename Types::MatrixNode> roots(1);
+    typename Types::Search search{};
+    search.run_for_iterations(learner, actor, device, states, model, roots);
+    std::vector<double> s{double(roots[0].count_matrix_nodes()), double(roots[0].stats.visits),
+                          double(roots[0].stats.value_total.get_row_value())};
+    for (auto v : roots[0].stats.row_visits) s.push_back(v);
+    for (auto v : roots[0].stats.col_visits) s.push_back(v);
+    return s;
+}
+
+static void test_search_callers() {
+    const auto a = tree_bandit_root<TreeBandit<Exp3<RefTree>>>(1024);
+    const auto b = tree_bandit_root<TreeBandit<Exp3<GpuTree>>>(1024);
+    CHECK(a == b);
+    std::printf("TreeBandit<Exp3>: nodes %.0f visits %.0f value_total %.1f  (ref)  vs  %.0f %.0f %.1f  (gpu)\n", a[0],
+                a[1], a[2], b[0], b[1], b[2]);
+    const auto c = off_policy_root<OffPolicy<Exp3<RefTree>>>(16, 256);
+    const auto d = off_policy_root<OffPolicy<Exp3<GpuTree>>>(16, 256);
+    CHECK(c == d);
+    std::printf("OffPolicy<Exp3>:  nodes %.0f visits %.0f value_total %.1f  (ref)  vs  %.0f %.0f %.1f  (gpu)\n", c[0],
+                c[1], c[2], d[0], d[1], d[2]);
+}
+
+// Copies of a model share the GPU context and evaluate concurrently from threads
+// (multithreaded.hh:112-113 gives every thread its own Model copy).
+static void test_threaded_copies() {
+    GpuTree::Model proto{prng{2}};
+    const RandomTree<>::State root{prng{4}, 8, 3, 3, 2};
+    std::vector<std::vector<double>> got(4);
+    std::vector<std::thread> pool;
+    for (int t = 0; t < 4; ++t)
+        pool.emplace_back([&, t] {
+            GpuTree::Model mine{proto};
+            for (int i = 0; i < 50; ++i) {
+                GpuTree::ModelOutput o;
+                mine.inference(RandomTree<>::State{root}, o);
+                got[t].push_back(o.value.get_row_value());
+            }
+        });
+    for (auto &th : pool) th.join();
+    RefTree::Model ref{prng{2}};
+    std::vector<double> want;
+    for (int i = 0; i < 50; ++i) {
+        RefTree::ModelOutput o;
+        ref.inference(RandomTree<>::State{root}, o);
+        want.push_back(o.value.get_row_value());
+    }
+    for (int t = 0; t < 4; ++t) CHECK(got[t] == want); /* same start state in every copy (Appendix C8) */
+    std::printf("threaded copies ok\n");
+}
+
+int main(int argc, char **argv) {
+    const bool gpu = argc > 1 && !std::strcmp(argv[1], "--gpu");
+    test_engine_access();
+    test_stream_locator();
+    if (!gpu) {
+        test_loud_failure_without_gpu();
+    } else {
+        try {
+            test_single_inference();
+            test_batch_inference();
+            test_search_callers();
+            test_threaded_copies();
+        } catch (const std::exception &e) {
+            std::printf("FAIL exception: %s\n", e.what());
+            ++g_failures;
+        }
+    }
+    std::printf(g_failures ? "FAILED (%d)\n" : "ALL OK\n", g_failures);
+    return g_failures ? 1 : 0;
+}
