@@ -97,6 +97,9 @@ typedef struct {
 void pcu_mt_seed(uint64_t seed, uint32_t *mt_x, uint32_t *mt_p);
 int pcu_mt_discard(uint32_t *mt_x, uint32_t *mt_p, uint64_t n);
 uint32_t pcu_mt_next(uint32_t *mt_x, uint32_t *mt_p);
+/* Diagnostic: the engine advanced by c * stride draws through the cached polynomial family
+ * x^(c * stride) mod phi that the device jump-ahead uses for its checkpoints (c < 65536). */
+int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint64_t c);
 
 /* ---- RandomTree batch -----------------------------------------------------------
  * Structure-of-arrays image of n RandomTree::State objects (random-tree.hh:14-27).

@@ -15,7 +15,7 @@ PKG = Path(__file__).resolve().parent
 ROOT = PKG.parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libpinyon_cuda.so"
-SOURCES = [CSRC / "pinyon_cuda.cu", CSRC / "mt_jump.cu"]
+SOURCES = [CSRC / "pinyon_cuda.cu", CSRC / "mt_jump.cu", CSRC / "mt_poly.cpp"]
 HEADERS = [CSRC / "kernels.cuh", CSRC / "mt19937.cuh", CSRC / "mt_jump.h", ROOT / "include" / "pinyon_cuda.h"]
 
 NVCC_FLAGS = [

@@ -30,7 +30,7 @@ HASH_MUL = 16777619
 # every symbol include/pinyon_cuda.h declares
 EXPORTS = [
     "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches", "pcu_last_kernel_ms",
-    "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next",
+    "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next", "pcu_mt_discard_family",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
 ]
 
@@ -104,6 +104,7 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_mt_seed.argtypes = [u64, vp, vp]
     lib.pcu_mt_seed.restype = None
     lib.pcu_mt_discard.argtypes = [vp, vp, u64]
+    lib.pcu_mt_discard_family.argtypes = [vp, vp, u64, u64]
     lib.pcu_mt_next.argtypes = [vp, vp]
     lib.pcu_mt_next.restype = u32
     lib.pcu_rollout_random_tree.argtypes = [vp, C.POINTER(RtBatch), C.POINTER(ModelRng), C.POINTER(Out)]

@@ -5,10 +5,12 @@
 // of that stream, the engine state must be advanced by D draws in O(1) kernels:
 // with phi the characteristic polynomial of the MT19937 transition (degree 19937)
 // and g = x^D mod phi,   X[D + j] = XOR_{i : g_i = 1} X[i + j]   for the raw state
-// word sequence X.  Host side: phi by Berlekamp–Massey on the engine's own output,
-// chains P_j = x^(unit * 2^j) mod phi by repeated squaring (cached per unit).
-// Device side: a doubling tree — level k turns windows 0..2^k-1 into windows
-// 2^k..2^(k+1)-1 with the single polynomial P_(j+k).
+// word sequence X.
+//   Host side (mt_poly.cpp): phi by Berlekamp–Massey on the engine's own output; the
+//     family g_c = x^(c * stride) mod phi, c = 0..count-1, cached per stride
+//     (g_2k = g_k^2, g_2k+1 = g_2k * g_1; PCLMULQDQ multiplies).
+//   Device side (mt_jump.cu): ONE extension of the base window to 20.6 K words and ONE
+//     launch in which CTA c applies g_c to it out of shared memory.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -17,30 +19,39 @@
 #include <vector>
 
 constexpr int MTJ_DEG = 19937;
+constexpr int MTJ_POLY_WORDS = 624;                  /* 19968 bits >= 19937 coefficients, as u32 */
 constexpr int MTJ_GROUPS = 90;                       /* 90 * 224 = 20160 >= 19937 extension words */
-constexpr int MTJ_EXT_LEN = 624 + MTJ_GROUPS * 224;  /* words of sequence per source window */
+constexpr int MTJ_EXT_LEN = 624 + MTJ_GROUPS * 224;  /* words of sequence generated from the base window */
+
+/* True once phi has been recovered (always, unless the host arithmetic is broken). */
+bool mt_jump_ready();
 
 /* x^n mod phi applied to a 624-word window on the host (any n).  false on failure. */
 bool mt_jump_host(uint32_t *window, uint64_t n);
 
-/* Set-bit exponents (ascending) of x^(unit_words * 2^j) mod phi; computed once and cached. */
-const std::vector<uint16_t> &mt_jump_poly(uint64_t unit_words, int j);
+/* The same through the cached family of `stride`: window advanced by c * stride draws. */
+bool mt_jump_host_family(uint32_t *window, uint64_t stride, uint64_t c);
+
+/* Bitmaps (MTJ_POLY_WORDS u32 each, bit i = coefficient of x^i) of x^(c * stride) mod phi
+ * for c = 0..count-1; computed once per stride and cached process-wide. */
+bool mt_jump_polys(uint64_t stride, uint64_t count, std::vector<uint32_t> &bitmaps);
 
 struct MtJump {
-    /* device copies of the position lists, keyed by (unit, j) */
-    struct DevPoly {
-        uint64_t unit;
-        int j;
-        uint16_t *pos;
-        uint32_t count;
+    /* device copies of polynomial families, keyed by stride */
+    struct DevFamily {
+        uint64_t stride;
+        uint64_t count;
+        uint32_t *bits;
+        uint64_t last_use;
     };
-    std::vector<DevPoly> polys;
+    std::vector<DevFamily> families;
+    uint64_t tick = 0;
     uint32_t *d_ext = nullptr;
-    size_t ext_cap = 0; /* windows */
 
-    /* Fill d_ck[c] (c = 0..count-1) with the window preceding draw c * unit_words * 2^j,
-     * d_ck[0] being `base_window` itself (host pointer). */
-    int run(cudaStream_t stream, const uint32_t *base_window, uint64_t count, uint64_t unit_words, int j,
-            uint32_t *d_ck, uint64_t *launches, std::string *err);
+    /* Fill d_ck[c] (c = 0..count-1) with the window preceding draw c * stride, d_ck[0]
+     * being `base_window` itself.  base_window must stay valid until the stream has consumed
+     * it (pinned staging memory).  Asynchronous on `stream` unless a family has to be built. */
+    int run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t count, uint64_t stride, uint32_t *d_ck,
+            uint64_t *launches, std::string *err);
     void release();
 };

@@ -38,6 +38,8 @@ struct DevBuf {
     }
 };
 
+constexpr int PIN_BASE_WINDOW = 1024; /* word offset in pin_small of the staged base window */
+
 enum BufId {
     B_STATE_SEED, B_STATE_POS, B_TSEED, B_DEPTH, B_BIAS, B_MSEED, B_PAYOFF, B_TRAJ, B_HASH, B_SUMS,
     B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_COUNT
@@ -295,25 +297,26 @@ int finish_all(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od, p
 /* Fill B_CKPT with `count` windows: window c holds the 624 raw words preceding model
  * draw number c * unit_words * 2^j, counted from the engine's next draw. */
 int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t count, uint64_t unit_words, int j) {
-    std::vector<uint32_t> win(MT_N);
-    host_window_from_engine(mt_x, mt_p, win.data());
+    uint32_t *win = ctx->pin_small + PIN_BASE_WINDOW; /* pinned: the upload below needs no host sync */
+    host_window_from_engine(mt_x, mt_p, win);
     CU(ctx->buf[B_CKPT].ensure(sizeof(uint32_t) * MT_N * (count + 1)));
     CU(ctx->buf[B_ENDWIN].ensure(sizeof(uint32_t) * MT_N));
     uint32_t *d_ck = reinterpret_cast<uint32_t *>(ctx->buf[B_CKPT].p);
+    const uint64_t stride = unit_words << j;
     if (ctx->host_checkpoints && count > 1) {
         /* test hook: plain stepping on the host, the definition the jump kernels must match */
-        const uint64_t stride = unit_words << j;
         std::vector<uint32_t> all((size_t)MT_N * count);
+        std::vector<uint32_t> w(win, win + MT_N);
         for (uint64_t c = 0; c < count; ++c) {
-            memcpy(all.data() + (size_t)MT_N * c, win.data(), sizeof(uint32_t) * MT_N);
-            if (c + 1 < count) host_window_advance(win.data(), stride);
+            memcpy(all.data() + (size_t)MT_N * c, w.data(), sizeof(uint32_t) * MT_N);
+            if (c + 1 < count) host_window_advance(w.data(), stride);
         }
         CU(cudaMemcpyAsync(d_ck, all.data(), sizeof(uint32_t) * MT_N * count, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream)); /* `all` is pageable and about to go out of scope */
         return PCU_OK;
     }
     std::string jerr;
-    if (ctx->jump.run(ctx->stream, win.data(), count, unit_words, j, d_ck, &ctx->launches, &jerr) != 0)
+    if (ctx->jump.run(ctx->stream, ctx->sms, win, count, stride, d_ck, &ctx->launches, &jerr) != 0)
         return fail(ctx, PCU_ERR_CUDA, "jump-ahead failed: %s", jerr.c_str());
     return PCU_OK;
 }
@@ -658,6 +661,15 @@ int pcu_mt_discard(uint32_t *mt_x, uint32_t *mt_p, uint64_t n) {
     uint32_t win[MT_N];
     host_window_from_engine(mt_x, *mt_p, win);
     if (!mt_jump_host(win, n)) return PCU_ERR_NOMEM;
+    engine_from_window(win, mt_x, mt_p);
+    return PCU_OK;
+}
+
+int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint64_t c) {
+    if (!mt_x || !mt_p || *mt_p > MT_N || c >= 65536) return PCU_ERR_INVALID;
+    uint32_t win[MT_N];
+    host_window_from_engine(mt_x, *mt_p, win);
+    if (!mt_jump_host_family(win, stride, c)) return PCU_ERR_NOMEM;
     engine_from_window(win, mt_x, mt_p);
     return PCU_OK;
 }

@@ -91,6 +91,29 @@ def test_host_jump_ahead_matches_stepping(oracle, n):
     assert got == [e2.next() for _ in range(1300)]
 
 
+def test_jump_family_matches_stepping(oracle):
+    """The polynomial family x^(c * stride) mod phi the device jump-ahead uploads (squarings,
+    carry-less multiplies, threaded level fill) must land every checkpoint where plain stepping
+    does.  stride = 4 words * depth 10 * 224 rollouts, the unit of BASELINE configs[1]."""
+    from pinyon_b200.capi import load_library
+
+    lib = load_library()
+    stride = 4 * 10 * 224
+    for c in (0, 1, 2, 3, 5, 8, 31, 64, 77, 100):  # grows the cached family across several levels
+        e = Engine(11)
+        e.next()
+        assert lib.pcu_mt_discard_family(e.x.ctypes.data, e.p.ctypes.data, stride, c) == 0
+        exp = np.zeros(700, np.uint32)
+        oracle.orc_mt_words(11, 1 + c * stride, 700, exp.ctypes.data)
+        assert [e.next() for _ in range(700)] == exp.tolist(), c
+    # a large stride (2^24 rollouts over 592 CTAs) composes with pcu_mt_discard
+    big = 4 * 10 * 224 * 128
+    e = Engine(5)
+    assert lib.pcu_mt_discard_family(e.x.ctypes.data, e.p.ctypes.data, big, 591) == 0
+    f = Engine(5).discard(591 * big)
+    assert [e.next() for _ in range(700)] == [f.next() for _ in range(700)]
+
+
 def test_window_reconstruction_every_position(oracle):
     """The jump path rebuilds the 624 words preceding the next draw from libstdc++'s (x, p)
     image for any p; check positions across a block against stepping."""
