@@ -57,12 +57,12 @@ int pcu_version(void);
 int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream);
 /* Number of kernels launched by this context since creation (bench.py gpu_launches). */
 uint64_t pcu_kernel_launches(const pcu_ctx *ctx);
-/* Device time in ms of the rollout kernel (k_stream / k_warp) of the last rollout call,
+/* Device time in ms of the rollout kernel (k_stream2 / k_warp) of the last rollout call,
  * from CUDA events recorded on the launching stream around that launch; -1 if none. */
 double pcu_last_kernel_ms(pcu_ctx *ctx);
-/* Tuning knobs, mainly for benchmarks: key "ctas_per_sm" (1..8) sets the number of
- * model-stream chunks per SM of the fused stream kernels.  Returns PCU_ERR_INVALID
- * for unknown keys. */
+/* Tuning knobs, mainly for benchmarks: key "streams_per_sm" (1..16, default 4) sets how many
+ * model-stream generator warps the fused kernels keep resident per SM (each needs one
+ * jump-ahead checkpoint per call).  Returns PCU_ERR_INVALID for unknown keys. */
 int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value);
 /* Pinned host memory for batch inputs/outputs (optional; any host pointer works). */
 void *pcu_host_alloc(pcu_ctx *ctx, size_t bytes);

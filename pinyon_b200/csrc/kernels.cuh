@@ -1,14 +1,14 @@
 // sm_100a rollout kernels of libpinyon_cuda.  See DESIGN.md "Kernels".
 //
-// k_stream      fused hot path: one MT19937 model stream per CTA, generated 224 words
-//               at a time by 224 threads (the recurrence X[n] = X[n-227] ^ f(X[n-624],
-//               X[n-623]) allows 227 independent words), reduced in-register to joint
-//               action codes, staged in shared memory and consumed one rollout per
-//               thread against a shared-memory table of the (shared) state stream.
-// k_gen_codes   the same generator writing action codes to global memory, for
-//               batches the fused kernel does not take (ragged depth, private states).
+// k_stream2     (stream.cuh) fused hot path: warp-per-stream MT19937 model generator
+//               feeding consumer warps that play one rollout per lane against a
+//               shared-memory table of the (shared) state stream.
+// k_gen_codes2  (stream.cuh) the same generator writing action codes to global memory,
+//               for batches the fused kernel does not take (ragged depth, private states).
 // k_warp        general path: one rollout per warp, the state's private MT19937 in
 //               shared memory, advanced 32 words per step by the warp.
+// The 224-thread CTA-wide generator below (GenAddr, gen_raw) only serves the jump-ahead's
+// k_jump_extend.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -24,31 +24,6 @@ constexpr int RING_WORDS = 4 * GEN_THREADS; /* 896 >= 624 + 224: four group slot
 constexpr int STEPS_PER_GROUP = GEN_THREADS / 4; /* a step = 2 random_int = 4 words */
 
 enum { KIND_TREE = 0, KIND_MOLD = 1 };
-
-struct StreamParams {
-    uint64_t n;      /* rollouts */
-    uint64_t chunk;  /* rollouts per CTA, multiple of 224 */
-    uint32_t depth;  /* uniform depth_bound / max_depth */
-    uint32_t cols, T, gen_words;
-    ModConst mrow, mcol;
-    const uint32_t *checkpoints; /* [ctas][624] raw words preceding each CTA's first model word */
-    const uint8_t *tab;          /* state-stream table: low nibble u64%10, bits 4-5 u64%3 at each draw index */
-    uint32_t tab_base, tab_len;
-    const uint32_t *state_pos;
-    uint32_t state_pos_u;
-    const int32_t *bias;
-    int32_t bias_u;
-    double pu;
-    int32_t thr_p, thr_q;
-    const double *fq; /* fq[n * fq_w + S] = (double)(float)(n / (double)S) */
-    uint32_t fq_w;
-    uint8_t *payoff;
-    uint8_t *traj;
-    uint32_t traj_stride;
-    uint32_t *traj_hash;
-    unsigned long long *sums;
-    uint32_t *end_window; /* [624] raw words preceding the first model word after the batch */
-};
 
 __device__ __forceinline__ uint32_t hash_step(uint32_t h, uint32_t joint, uint32_t chance) {
     return (h ^ (joint | (chance << 16))) * PCU_HASH_MUL;
@@ -87,22 +62,6 @@ __device__ __forceinline__ void load_checkpoint(uint32_t *ring, const uint32_t *
     for (int i = t; i < MT_N; i += GEN_THREADS) ring[48 + i] = ckpt[i];
 }
 
-/* One group: every thread produces one stream word; lanes 4q..4q+3 hold the words of
- * step q (row hi, row lo, col hi, col lo — uniform_64 draws HIGH first, random.hh:28).
- * Returns the joint action code row*cols+col on lanes with (t & 3) == 0. */
-template <int PH>
-__device__ __forceinline__ uint32_t gen_group(uint32_t *ring, const GenAddr &g, uint32_t cols) {
-    const uint32_t a = ring[g.ra[PH]], b = ring[g.rb[PH]], c = ring[g.rc[PH]];
-    const uint32_t x = mt_twist(a, b, c);
-    ring[g.wa[PH]] = x;
-    const uint32_t z = mt_temper(x);
-    const uint32_t m = mod32(z, g.n, g.m);
-    const uint32_t lo = __shfl_down_sync(PCU_FULL, m, 1);
-    const uint32_t v = mod32(m * g.c32 + lo, g.n, g.m);
-    const uint32_t cc = __shfl_down_sync(PCU_FULL, v, 2);
-    return v * cols + cc;
-}
-
 /* The raw (untempered) word only — used by the jump-ahead extension kernel. */
 template <int PH>
 __device__ __forceinline__ uint32_t gen_raw(uint32_t *ring, const GenAddr &g) {
@@ -112,242 +71,7 @@ __device__ __forceinline__ uint32_t gen_raw(uint32_t *ring, const GenAddr &g) {
     return x;
 }
 
-/* The 624 raw words preceding stream word `w_end`, counted from the start of the current
- * 896-word-aligned generation pass (ring slot of word n' is (n' + 672) mod 896). */
-__device__ __forceinline__ void dump_window(const uint32_t *ring, uint32_t w_end, uint32_t *dst, int t) {
-    for (int i = t; i < MT_N; i += GEN_THREADS) dst[i] = ring[(w_end + 48 + i) % RING_WORDS];
-}
-
-template <int KIND, typename CodeT, bool TAB_SMEM>
-__global__ void __launch_bounds__(GEN_THREADS) k_stream(const StreamParams P) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint32_t *ring = reinterpret_cast<uint32_t *>(smem_raw);
-    CodeT *codes = reinterpret_cast<CodeT *>(ring + RING_WORDS);
-    const int t = threadIdx.x;
-    const uint32_t d = P.depth;
-    const uint64_t first = (uint64_t)blockIdx.x * P.chunk;
-    if (first >= P.n) return;
-    const uint64_t last = (first + P.chunk < P.n) ? first + P.chunk : P.n;
-
-    const uint8_t *tab = P.tab;
-    if (KIND == KIND_TREE && TAB_SMEM) {
-        uint8_t *stab = reinterpret_cast<uint8_t *>(codes + (size_t)GEN_THREADS * d);
-        stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
-        for (uint32_t i = t; i < P.tab_len; i += GEN_THREADS) stab[i] = P.tab[i];
-        tab = stab;
-    }
-    load_checkpoint(ring, P.checkpoints + (size_t)blockIdx.x * MT_N, t);
-    const GenAddr g = make_gen_addr(t, P.mrow, P.mcol);
-    const bool writer = (t & 3) == 0;
-    const uint32_t q0 = t >> 2;
-    __syncthreads();
-
-    unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_n = 0;
-
-    for (uint64_t base = first; base < last; base += GEN_THREADS) {
-        /* ---- generate this round's steps: 4*d groups (224*d steps) for a full round, only
-         * the groups its rollouts need for the ragged last one */
-        const uint32_t live = (last - base < GEN_THREADS) ? (uint32_t)(last - base) : GEN_THREADS;
-        const uint32_t groups = (live * d + STEPS_PER_GROUP - 1) / STEPS_PER_GROUP;
-        uint32_t q = q0;
-        for (uint32_t g4 = 0; g4 < (groups >> 2); ++g4) {
-            uint32_t code;
-            code = gen_group<0>(ring, g, P.cols);
-            if (writer) codes[q] = (CodeT)code;
-            q += STEPS_PER_GROUP;
-            __syncthreads();
-            code = gen_group<1>(ring, g, P.cols);
-            if (writer) codes[q] = (CodeT)code;
-            q += STEPS_PER_GROUP;
-            __syncthreads();
-            code = gen_group<2>(ring, g, P.cols);
-            if (writer) codes[q] = (CodeT)code;
-            q += STEPS_PER_GROUP;
-            __syncthreads();
-            code = gen_group<3>(ring, g, P.cols);
-            if (writer) codes[q] = (CodeT)code;
-            q += STEPS_PER_GROUP;
-            __syncthreads();
-        }
-        if (groups & 3) { /* only ever in the batch's last round */
-            uint32_t code = gen_group<0>(ring, g, P.cols);
-            if (writer) codes[q] = (CodeT)code;
-            q += STEPS_PER_GROUP;
-            __syncthreads();
-            if ((groups & 3) > 1) {
-                code = gen_group<1>(ring, g, P.cols);
-                if (writer) codes[q] = (CodeT)code;
-                q += STEPS_PER_GROUP;
-                __syncthreads();
-            }
-            if ((groups & 3) > 2) {
-                code = gen_group<2>(ring, g, P.cols);
-                if (writer) codes[q] = (CodeT)code;
-                q += STEPS_PER_GROUP;
-                __syncthreads();
-            }
-        }
-        /* the engine state the host model must continue from: the window right after the
-         * batch's last model word (monte-carlo-model.hh:58-67 leaves `device` there) */
-        if (last == P.n && base + GEN_THREADS >= last && P.end_window) dump_window(ring, 4u * d * live, P.end_window, t);
-        /* ---- consume: thread t plays rollout base + t with steps codes[t*d .. t*d+d) */
-        const uint64_t i = base + t;
-        if (i < last) {
-            const CodeT *my = codes + (size_t)t * d;
-            uint32_t h = PCU_HASH_INIT;
-            uint32_t pay = 0;
-            uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
-            if (KIND == KIND_MOLD) {
-                for (uint32_t s = 0; s < d; ++s) {
-                    const uint32_t code = my[s];
-                    h = hash_step(h, code, 0);
-                    if (tr) {
-                        const uint32_t r = code / P.cols;
-                        tr[3 * s + 0] = (uint8_t)r;
-                        tr[3 * s + 1] = (uint8_t)(code - r * P.cols);
-                        tr[3 * s + 2] = 0;
-                    }
-                }
-                acc_d += 1;
-            } else {
-                uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
-                int bias = P.bias ? P.bias[i] : P.bias_u;
-                const uint32_t T = P.T;
-                if (T == 1) {
-                    for (uint32_t s = 0; s < d; ++s) {
-                        const uint32_t code = my[s];
-                        p += code; /* discard(row*cols + col): random-tree.hh:88-89 */
-                        bias += (int)((tab[p] >> 4) & 3u) - 1;
-                        p += 2 + P.gen_words;
-                        h = hash_step(h, code, 0);
-                        if (tr) {
-                            const uint32_t r = code / P.cols;
-                            tr[3 * s + 0] = (uint8_t)r;
-                            tr[3 * s + 1] = (uint8_t)(code - r * P.cols);
-                            tr[3 * s + 2] = 0;
-                        }
-                    }
-                } else {
-                    uint32_t gb = p - P.gen_words; /* where the current chance strategies were drawn */
-                    for (uint32_t s = 0; s < d; ++s) {
-                        const uint32_t code = my[s];
-                        const uint32_t st = code * T;
-                        const uint8_t *cell = tab + gb + 2 * st;
-                        int S = 0;
-                        for (uint32_t k = 0; k < T; ++k) {
-                            int nk = (int)(cell[2 * k] & 15u) + 1;
-                            if (nk * P.thr_q < P.thr_p * 10) nk = 0;
-                            S += nk;
-                        }
-                        const bool fallback = (S == 0);
-                        if (fallback) S = 1;
-                        double pp = P.pu;
-                        uint32_t ch = 0;
-                        for (uint32_t k = 0; k < T; ++k) {
-                            int nk = (int)(cell[2 * k] & 15u) + 1;
-                            if (nk * P.thr_q < P.thr_p * 10) nk = 0;
-                            if (fallback && k == 0) nk = 1;
-                            pp -= __ldg(P.fq + (uint32_t)nk * P.fq_w + (uint32_t)S);
-                            if (pp <= 0) {
-                                ch = k;
-                                break;
-                            }
-                        }
-                        p += st + ch;
-                        bias += (int)((tab[p] >> 4) & 3u) - 1;
-                        p += 2;
-                        gb = p;
-                        p += P.gen_words;
-                        h = hash_step(h, code, ch);
-                        if (tr) {
-                            const uint32_t r = code / P.cols;
-                            tr[3 * s + 0] = (uint8_t)r;
-                            tr[3 * s + 1] = (uint8_t)(code - r * P.cols);
-                            tr[3 * s + 2] = (uint8_t)ch;
-                        }
-                    }
-                }
-                pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
-                acc_w += (pay == 2);
-                acc_d += (pay == 1);
-                acc_l += (pay == 0);
-            }
-            if (tr)
-                for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
-            if (P.payoff) P.payoff[i] = (uint8_t)pay;
-            if (P.traj_hash) P.traj_hash[i] = h;
-            acc_h += h;
-            acc_n += 1;
-        }
-        __syncthreads();
-    }
-    if (P.sums) {
-        acc_w = warp_sum_u64(acc_w);
-        acc_d = warp_sum_u64(acc_d);
-        acc_l = warp_sum_u64(acc_l);
-        acc_h = warp_sum_u64(acc_h);
-        acc_n = warp_sum_u64(acc_n);
-        if ((t & 31) == 0) {
-            if (acc_w) atomicAdd(P.sums + 0, acc_w);
-            if (acc_d) atomicAdd(P.sums + 1, acc_d);
-            if (acc_l) atomicAdd(P.sums + 2, acc_l);
-            atomicAdd(P.sums + 3, acc_n * d);
-            atomicAdd(P.sums + 4, acc_h);
-        }
-    }
-}
-
-/* ------------------------------------------------------------------ k_gen_codes */
-
-struct GenParams {
-    uint64_t total_steps;
-    uint64_t chunk_steps; /* steps per CTA, multiple of 224 */
-    uint32_t cols;
-    ModConst mrow, mcol;
-    const uint32_t *checkpoints;
-    void *codes; /* CodeT[total_steps] */
-    uint32_t *end_window;
-};
-
-template <typename CodeT>
-__global__ void __launch_bounds__(GEN_THREADS) k_gen_codes(const GenParams P) {
-    __shared__ uint32_t ring[RING_WORDS];
-    const int t = threadIdx.x;
-    const uint64_t first = (uint64_t)blockIdx.x * P.chunk_steps;
-    if (first >= P.total_steps) return;
-    const uint64_t last = (first + P.chunk_steps < P.total_steps) ? first + P.chunk_steps : P.total_steps;
-    load_checkpoint(ring, P.checkpoints + (size_t)blockIdx.x * MT_N, t);
-    const GenAddr g = make_gen_addr(t, P.mrow, P.mcol);
-    const bool writer = (t & 3) == 0;
-    CodeT *codes = reinterpret_cast<CodeT *>(P.codes);
-    __syncthreads();
-    for (uint64_t qb = first; qb < last; qb += 4 * STEPS_PER_GROUP) { /* uniform trip count: barriers inside */
-        const uint64_t q = qb + (t >> 2);
-        const uint32_t live = (last - qb < 4 * STEPS_PER_GROUP) ? (uint32_t)(last - qb) : 4 * STEPS_PER_GROUP;
-        const uint32_t groups = (live + STEPS_PER_GROUP - 1) / STEPS_PER_GROUP; /* 1..4 */
-        uint32_t code;
-        code = gen_group<0>(ring, g, P.cols);
-        if (writer && q < last) codes[q] = (CodeT)code;
-        __syncthreads();
-        if (groups > 1) {
-            code = gen_group<1>(ring, g, P.cols);
-            if (writer && q + STEPS_PER_GROUP < last) codes[q + STEPS_PER_GROUP] = (CodeT)code;
-            __syncthreads();
-        }
-        if (groups > 2) {
-            code = gen_group<2>(ring, g, P.cols);
-            if (writer && q + 2 * STEPS_PER_GROUP < last) codes[q + 2 * STEPS_PER_GROUP] = (CodeT)code;
-            __syncthreads();
-        }
-        if (groups > 3) {
-            code = gen_group<3>(ring, g, P.cols);
-            if (writer && q + 3 * STEPS_PER_GROUP < last) codes[q + 3 * STEPS_PER_GROUP] = (CodeT)code;
-            __syncthreads();
-        }
-        if (last == P.total_steps && qb + 4 * STEPS_PER_GROUP >= last && P.end_window)
-            dump_window(ring, 4u * live, P.end_window, t);
-    }
-}
+#include "stream.cuh"
 
 /* ----------------------------------------------------------------------- k_warp */
 

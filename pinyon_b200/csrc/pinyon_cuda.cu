@@ -57,7 +57,7 @@ struct pcu_ctx {
     std::string err;
     std::string path;
     uint64_t launches = 0;
-    int ctas_per_sm = 4;
+    int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
     int host_checkpoints = 0; /* test hook: brute-force checkpoints on the host instead of the jump kernels */
     DevBuf buf[B_COUNT];
@@ -295,14 +295,13 @@ int finish_all(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od, p
 /* ------------------------------------------------ model-stream checkpoints */
 
 /* Fill B_CKPT with `count` windows: window c holds the 624 raw words preceding model
- * draw number c * unit_words * 2^j, counted from the engine's next draw. */
-int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t count, uint64_t unit_words, int j) {
+ * draw number c * stride, counted from the engine's next draw. */
+int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t count, uint64_t stride) {
     uint32_t *win = ctx->pin_small + PIN_BASE_WINDOW; /* pinned: the upload below needs no host sync */
     host_window_from_engine(mt_x, mt_p, win);
     CU(ctx->buf[B_CKPT].ensure(sizeof(uint32_t) * MT_N * (count + 1)));
     CU(ctx->buf[B_ENDWIN].ensure(sizeof(uint32_t) * MT_N));
     uint32_t *d_ck = reinterpret_cast<uint32_t *>(ctx->buf[B_CKPT].p);
-    const uint64_t stride = unit_words << j;
     if (ctx->host_checkpoints && count > 1) {
         /* test hook: plain stepping on the host, the definition the jump kernels must match */
         std::vector<uint32_t> all((size_t)MT_N * count);
@@ -335,21 +334,26 @@ int fetch_end_window(pcu_ctx *ctx) {
     return PCU_OK;
 }
 
-/* Work is cut into 224 * 2^j units per CTA so that every checkpoint stride is one of the
- * cached polynomials x^(unit * 2^j); j is the smallest that fits the CTA budget. */
-int pick_shift(uint64_t units224, int sms, int ctas_per_sm) {
-    const uint64_t budget = (uint64_t)sms * ctas_per_sm;
-    int j = 0;
-    while (((units224 + (1ull << j) - 1) >> j) > budget) ++j;
-    return j;
+/* Work per model stream (one generator warp).  Every distinct stride needs its own family of
+ * jump polynomials (cached, ~80 ms to build), so chunk sizes are quantised to four significant
+ * bits: at most 1/16 of the stream slots idle, a bounded set of strides per depth. */
+uint64_t pick_chunk(uint64_t units, uint64_t slots, uint64_t min_chunk) {
+    uint64_t c = (units + slots - 1) / slots;
+    if (c < min_chunk) c = min_chunk;
+    if (c < 32) return c;
+    int e = 0;
+    while ((c >> e) >= 32) ++e; /* c >> e in [16, 32) */
+    const uint64_t m = (c + (1ull << e) - 1) >> e;
+    return m << e;
 }
 
 template <int KIND, typename CodeT>
-int launch_stream(pcu_ctx *ctx, const StreamParams &P, uint64_t ctas, bool tab_smem, size_t smem) {
-    auto kern = tab_smem ? k_stream<KIND, CodeT, true> : k_stream<KIND, CodeT, false>;
+int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t smem) {
+    auto kern = tab_smem ? k_stream2<KIND, CodeT, true> : k_stream2<KIND, CodeT, false>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned ctas = (P.streams + GW_PAIRS - 1) / GW_PAIRS;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    kern<<<(unsigned)ctas, GEN_THREADS, smem, ctx->stream>>>(P);
+    kern<<<ctas, GW_PAIRS * 64, smem, ctx->stream>>>(P);
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->ev_valid = true;
     ctx->launches++;
@@ -361,13 +365,13 @@ constexpr size_t SMEM_LIMIT = 200 * 1024;
 
 /* Fused path (mode S, uniform depth, shared or absent state stream). */
 template <int KIND>
-int run_stream(pcu_ctx *ctx, StreamParams &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od) {
+int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od) {
     const uint64_t n = P.n;
-    const uint64_t rounds = (n + GEN_THREADS - 1) / GEN_THREADS;
-    const int j = pick_shift(rounds, ctx->sms, ctx->ctas_per_sm);
-    P.chunk = (uint64_t)GEN_THREADS << j;
-    const uint64_t ctas = (n + P.chunk - 1) / P.chunk;
-    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, ctas, 4ull * P.depth * GEN_THREADS, j);
+    const uint64_t slots = (uint64_t)ctx->sms * ctx->streams_per_sm;
+    P.chunk = pick_chunk(n, slots, 128);
+    P.streams = (uint32_t)((n + P.chunk - 1) / P.chunk);
+    P.rb = (32u * P.depth >= (uint32_t)GW_STEPS) ? 32u : 64u; /* a group of 56 codes may span two buffers at most */
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, P.streams, 4ull * P.depth * P.chunk);
     if (rc) return rc;
     P.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
     P.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
@@ -376,8 +380,8 @@ int run_stream(pcu_ctx *ctx, StreamParams &P, uint32_t rows, pcu_model_rng *rng,
     P.traj_hash = od.hash;
     P.sums = od.sums;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
-    const size_t code_bytes = (size_t)GEN_THREADS * P.depth * (code8 ? 1 : 2);
-    size_t smem = RING_WORDS * 4 + code_bytes + 16;
+    const size_t queue_bytes = (size_t)GW_PAIRS * 2 * P.rb * P.depth * (code8 ? 1 : 2);
+    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + (size_t)P.fq_len * 8 + queue_bytes + 16;
     bool tab_smem = false;
     if (KIND == KIND_TREE && smem + P.tab_len + 16 <= SMEM_LIMIT) {
         tab_smem = true;
@@ -385,9 +389,9 @@ int run_stream(pcu_ctx *ctx, StreamParams &P, uint32_t rows, pcu_model_rng *rng,
     }
     if (smem > SMEM_LIMIT) return fail(ctx, PCU_ERR_UNSUPPORTED, "depth %u needs %zu B of shared memory", P.depth, smem);
     if (code8)
-        rc = launch_stream<KIND, uint8_t>(ctx, P, ctas, tab_smem, smem);
+        rc = launch_stream<KIND, uint8_t>(ctx, P, tab_smem, smem);
     else
-        rc = launch_stream<KIND, uint16_t>(ctx, P, ctas, tab_smem, smem);
+        rc = launch_stream<KIND, uint16_t>(ctx, P, tab_smem, smem);
     if (rc) return rc;
     return fetch_end_window(ctx);
 }
@@ -396,18 +400,17 @@ int run_stream(pcu_ctx *ctx, StreamParams &P, uint32_t rows, pcu_model_rng *rng,
 int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, pcu_model_rng *rng, bool *code16) {
     const bool c16 = (uint64_t)rows * cols > 256;
     *code16 = c16;
-    const uint64_t units = (total_steps + GEN_THREADS - 1) / GEN_THREADS;
-    int j = pick_shift(units, ctx->sms, ctx->ctas_per_sm);
-    if (j < 6) j = 6; /* small batches: few CTAs, few jumps */
-    const uint64_t chunk = (uint64_t)GEN_THREADS << j;
-    uint64_t ctas = (total_steps + chunk - 1) / chunk;
-    if (ctas == 0) ctas = 1;
-    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, ctas, 4ull * GEN_THREADS, j);
+    const uint64_t slots = (uint64_t)ctx->sms * ctx->streams_per_sm;
+    const uint64_t chunk = pick_chunk(total_steps ? total_steps : 1, slots, 4096); /* steps per stream */
+    uint64_t streams = (total_steps + chunk - 1) / chunk;
+    if (streams == 0) streams = 1;
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, streams, 4ull * chunk);
     if (rc) return rc;
     CU(ctx->buf[B_CODES].ensure((total_steps + 8) * (c16 ? 2 : 1)));
-    GenParams G;
+    Gen2Params G;
     G.total_steps = total_steps;
     G.chunk_steps = chunk;
+    G.streams = (uint32_t)streams;
     G.cols = cols;
     G.mrow = make_mod_const(rows);
     G.mcol = make_mod_const(cols);
@@ -415,10 +418,11 @@ int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, 
     G.codes = ctx->buf[B_CODES].p;
     G.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
     if (total_steps == 0) return PCU_OK; /* engine untouched */
+    const unsigned ctas = (unsigned)((streams + 3) / 4);
     if (c16)
-        k_gen_codes<uint16_t><<<(unsigned)ctas, GEN_THREADS, 0, ctx->stream>>>(G);
+        k_gen_codes2<uint16_t><<<ctas, 128, 0, ctx->stream>>>(G);
     else
-        k_gen_codes<uint8_t><<<(unsigned)ctas, GEN_THREADS, 0, ctx->stream>>>(G);
+        k_gen_codes2<uint8_t><<<ctas, 128, 0, ctx->stream>>>(G);
     ctx->launches++;
     CU(cudaGetLastError());
     return fetch_end_window(ctx);
@@ -605,9 +609,9 @@ int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream) {
 
 int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     if (!ctx || !key) return PCU_ERR_INVALID;
-    if (!strcmp(key, "ctas_per_sm")) {
-        if (value < 1 || value > 8) return fail(ctx, PCU_ERR_INVALID, "ctas_per_sm must be 1..8");
-        ctx->ctas_per_sm = (int)value;
+    if (!strcmp(key, "streams_per_sm") || !strcmp(key, "ctas_per_sm")) { /* second name: r1a spelling */
+        if (value < 1 || value > 16) return fail(ctx, PCU_ERR_INVALID, "streams_per_sm must be 1..16");
+        ctx->streams_per_sm = (int)value;
         return PCU_OK;
     }
     if (!strcmp(key, "force_general")) {
@@ -749,7 +753,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
             ctx->tab_key.base = tab_base;
             ctx->tab_key.len = tab_len;
         }
-        StreamParams P;
+        Stream2Params P;
         memset(&P, 0, sizeof(P));
         P.n = n;
         P.depth = b->depth_u;
@@ -770,6 +774,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         P.thr_q = b->thr_q;
         P.fq = d_fq;
         P.fq_w = fq_w;
+        P.fq_len = (T > 1) ? 11u * fq_w : 0u;
         P.traj_stride = out->traj_stride;
         ctx->path = "stream_table";
         if ((rc = run_stream<KIND_TREE>(ctx, P, b->rows, rng, od))) return rc;
@@ -845,7 +850,7 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
 
     if (!ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && b->depth_u > 0) {
-        StreamParams P;
+        Stream2Params P;
         memset(&P, 0, sizeof(P));
         P.n = n;
         P.depth = b->depth_u;
