@@ -175,7 +175,8 @@ const char *pcu_last_path(const pcu_ctx *ctx);
 
 /* Integer-issue peak microbenchmark (eight cross-coupled chains per thread, best of
  * `reps`, CUDA events), the roofline denominator of SURVEY.md §8(d).  variant 0: LOP3
- * only; 1: LOP3 + SHF + IADD3 (ALU pipe); 2: LOP3 + SHF + IMAD (ALU + FMA pipes).
+ * only; 1: LOP3 + SHF + IADD3 (ALU pipe); 2: LOP3 + SHF + IMAD (ALU + FMA pipes); 3..6 are
+ * single-pipe and mixed probes (IMAD, IMAD.HI, LOP3:IMAD 1:1, LOP3:IMAD:IMAD.HI).
  * Writes int32 thread-operations per second. */
 int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_second);
 

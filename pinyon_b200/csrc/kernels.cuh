@@ -325,6 +325,14 @@ __device__ __forceinline__ uint32_t op_imad(uint32_t a, uint32_t b, uint32_t c) 
 
 constexpr int INT_PEAK_OPS_PER_ITER = 4 * 8 * 3;
 
+__device__ __forceinline__ uint32_t op_imadhi(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t d;
+    asm("mad.hi.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
+
+/* Variants 0..2 feed the roofline; 3..6 are pipe probes used to design the generator:
+ * 3: IMAD only; 4: IMAD.HI only; 5: LOP3, IMAD, LOP3 ... (2:1); 6: LOP3 + IMAD + IMAD.HI. */
 template <int VARIANT>
 __global__ void __launch_bounds__(256) k_int_peak(uint32_t *out, uint32_t seed, int iters) {
     uint32_t a[8];
@@ -345,10 +353,26 @@ __global__ void __launch_bounds__(256) k_int_peak(uint32_t *out, uint32_t seed, 
                     a[j] = op_lop3(a[j], nb, k1);
                     a[j] = op_shf(a[j], nb);
                     a[j] = op_iadd3(a[j], nb, k1);
-                } else {
+                } else if (VARIANT == 2) {
                     a[j] = op_lop3(a[j], nb, k1);
                     a[j] = op_shf(a[j], nb);
                     a[j] = op_imad(a[j], k1, nb);
+                } else if (VARIANT == 3) {
+                    a[j] = op_imad(a[j], k1, nb);
+                    a[j] = op_imad(a[j], nb, k1);
+                    a[j] = op_imad(nb, a[j], k1);
+                } else if (VARIANT == 4) {
+                    a[j] = op_imadhi(a[j], k1, nb);
+                    a[j] = op_imadhi(a[j], nb, k1);
+                    a[j] = op_imadhi(nb, a[j], k1);
+                } else if (VARIANT == 5) {
+                    a[j] = op_lop3(a[j], nb, k1);
+                    a[j] = op_imad(a[j], k1, nb);
+                    a[j] = ((j + u) & 1) ? op_lop3(a[j], k1, nb) : op_imad(a[j], nb, k1);
+                } else {
+                    a[j] = op_lop3(a[j], nb, k1);
+                    a[j] = op_imadhi(a[j], k1, nb);
+                    a[j] = ((j + u) & 1) ? op_lop3(a[j], k1, nb) : op_imad(a[j], nb, k1);
                 }
             }
         }

@@ -370,7 +370,9 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     const uint64_t slots = (uint64_t)ctx->sms * ctx->streams_per_sm;
     P.chunk = pick_chunk(n, slots, 128);
     P.streams = (uint32_t)((n + P.chunk - 1) / P.chunk);
-    P.rb = (32u * P.depth >= (uint32_t)GW_STEPS) ? 32u : 64u; /* a group of 56 codes may span two buffers at most */
+    P.rb = 32;
+    P.qlen = 1024;
+    while (P.qlen < 2ull * P.rb * P.depth + 2 * GW_PASS_STEPS) P.qlen <<= 1;
     int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, P.streams, 4ull * P.depth * P.chunk);
     if (rc) return rc;
     P.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
@@ -380,8 +382,8 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.traj_hash = od.hash;
     P.sums = od.sums;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
-    const size_t queue_bytes = (size_t)GW_PAIRS * 2 * P.rb * P.depth * (code8 ? 1 : 2);
-    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + (size_t)P.fq_len * 8 + queue_bytes + 16;
+    const size_t queue_bytes = (size_t)GW_PAIRS * P.qlen * (code8 ? 1 : 2);
+    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + 2 * GW_PAIRS * 4 + (size_t)P.fq_len * 8 + queue_bytes + 16;
     bool tab_smem = false;
     if (KIND == KIND_TREE && smem + P.tab_len + 16 <= SMEM_LIMIT) {
         tab_smem = true;
@@ -910,12 +912,15 @@ int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_se
     double best = 0;
     for (int r = 0; r < reps + 1; ++r) {
         CU(cudaEventRecord(e0, ctx->stream));
-        if (variant == 0)
-            k_int_peak<0><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters);
-        else if (variant == 1)
-            k_int_peak<1><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters);
-        else
-            k_int_peak<2><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters);
+        switch (variant) {
+            case 0: k_int_peak<0><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 1: k_int_peak<1><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 2: k_int_peak<2><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 3: k_int_peak<3><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 4: k_int_peak<4><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 5: k_int_peak<5><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            default: k_int_peak<6><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+        }
         ctx->launches++;
         CU(cudaEventRecord(e1, ctx->stream));
         CU(cudaEventSynchronize(e1));

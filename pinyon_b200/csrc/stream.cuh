@@ -31,6 +31,7 @@ constexpr int GW_ACTIVE = 28;             /* generator lanes in use */
 constexpr int GW_STEPS = 2 * GW_ACTIVE;   /* model steps per group */
 constexpr int GW_WORDS = 4 * GW_STEPS;    /* 224 <= 227 */
 constexpr int GW_RING = 4 * GW_WORDS;     /* 896 >= 624 + 224: four group slots */
+constexpr int GW_PASS_STEPS = 4 * GW_STEPS; /* model steps per pass (one turn of the ring) */
 constexpr int GW_PAIRS = 4;               /* generator/consumer warp pairs per CTA */
 
 /* Ring slot of (compile-time offset C) + 4 * lane; the wrap test is only emitted for the
@@ -46,36 +47,50 @@ __device__ __forceinline__ int gw_slot(int l4) {
     }
 }
 
-/* The four words of one model step: stream word n' (counted from the start of the current
- * 896-word pass) lives in ring slot (n' + 672) mod 896, so X[n-624] is at n' + 48 and
- * X[n-227] at n' + 445.  Returns the tempered words. */
-template <int PH, int H>
-__device__ __forceinline__ void gw_step_words(uint32_t *ring, int l4, uint32_t &z0, uint32_t &z1, uint32_t &z2,
-                                              uint32_t &z3) {
-    constexpr int off = GW_WORDS * PH + (GW_WORDS / 2) * H;
-    const uint4 a = *reinterpret_cast<const uint4 *>(ring + gw_slot<off + 48>(l4));
-    const uint32_t a4 = ring[gw_slot<off + 52>(l4)];
-    const uint4 c = *reinterpret_cast<const uint4 *>(ring + gw_slot<off + 444>(l4)); /* X[n-228 .. n-225] */
-    const uint32_t c4 = ring[gw_slot<off + 448>(l4)];
+/* Operands of one group for one lane: both of its model steps (H = 0: step lane, H = 1: step
+ * 28 + lane).  Stream word n' (counted from the start of the current 896-word pass) lives in
+ * ring slot (n' + 672) mod 896, so X[n-624] is at n' + 48 and X[n-227] at n' + 445. */
+struct GwOps {
+    uint4 a0, c0, a1, c1; /* X[n-624 .. n-621], X[n-228 .. n-225] */
+    uint32_t a04, c04, a14, c14; /* X[n-620], X[n-224] */
+};
+
+template <int PH>
+__device__ __forceinline__ void gw_load(const uint32_t *ring, int l4, GwOps &o) {
+    constexpr int off0 = GW_WORDS * PH, off1 = off0 + GW_WORDS / 2;
+    o.a0 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off0 + 48>(l4));
+    o.a1 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off1 + 48>(l4));
+    o.c0 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off0 + 444>(l4));
+    o.c1 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off1 + 444>(l4));
+    o.a04 = ring[gw_slot<off0 + 52>(l4)];
+    o.a14 = ring[gw_slot<off1 + 52>(l4)];
+    o.c04 = ring[gw_slot<off0 + 448>(l4)];
+    o.c14 = ring[gw_slot<off1 + 448>(l4)];
+}
+
+__device__ __forceinline__ uint4 gw_twist4(const uint4 &a, uint32_t a4, const uint4 &c, uint32_t c4) {
     uint4 x;
     x.x = mt_twist(a.x, a.y, c.y);
     x.y = mt_twist(a.y, a.z, c.z);
     x.z = mt_twist(a.z, a.w, c.w);
     x.w = mt_twist(a.w, a4, c4);
-    *reinterpret_cast<uint4 *>(ring + gw_slot<off + 672>(l4)) = x;
-    z0 = mt_temper(x.x);
-    z1 = mt_temper(x.y);
-    z2 = mt_temper(x.z);
-    z3 = mt_temper(x.w);
+    return x;
 }
 
-template <int PH, int H>
-__device__ __forceinline__ uint32_t gw_step_code(uint32_t *ring, int l4, const ModConst &mrow, const ModConst &mcol,
-                                                 uint32_t cols) {
-    uint32_t z0, z1, z2, z3;
-    gw_step_words<PH, H>(ring, l4, z0, z1, z2, z3);
-    const uint32_t row = mod64(z0, z1, mrow);
-    const uint32_t col = mod64(z2, z3, mcol);
+template <int PH>
+__device__ __forceinline__ void gw_store(uint32_t *ring, int l4, bool active, const uint4 &x0, const uint4 &x1) {
+    constexpr int off0 = GW_WORDS * PH, off1 = off0 + GW_WORDS / 2;
+    if (active) {
+        *reinterpret_cast<uint4 *>(ring + gw_slot<off0 + 672>(l4)) = x0;
+        *reinterpret_cast<uint4 *>(ring + gw_slot<off1 + 672>(l4)) = x1;
+    }
+}
+
+/* Raw words of one step -> joint action code row * cols + col: temper, then the two
+ * random_int draws (uniform_64 takes the HIGH word first, random.hh:26,28). */
+__device__ __forceinline__ uint32_t gw_code(const uint4 &x, const ModConst &mrow, const ModConst &mcol, uint32_t cols) {
+    const uint32_t row = mod64(mt_temper(x.x), mt_temper(x.y), mrow);
+    const uint32_t col = mod64(mt_temper(x.z), mt_temper(x.w), mcol);
     return row * cols + col;
 }
 
@@ -88,10 +103,70 @@ __device__ __forceinline__ void gw_dump_window(const uint32_t *ring, uint32_t w_
     for (int i = lane; i < MT_N; i += 32) dst[i] = ring[(w_end + 48 + i) % GW_RING];
 }
 
-__device__ __forceinline__ void nb_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
-__device__ __forceinline__ void nb_arrive(int id) {
-    __threadfence_block();
-    asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
+/* Shared-memory flags between a generator warp and its consumer warp. */
+__device__ __forceinline__ void flag_release(uint32_t *flag, uint32_t v) {
+    asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(flag)), "r"(v)
+                 : "memory");
+}
+__device__ __forceinline__ uint32_t flag_acquire(const uint32_t *flag) {
+    uint32_t v;
+    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(flag)) : "memory");
+    return v;
+}
+
+/* The generator loop, software pipelined: while the 8 words of group g are tempered and reduced
+ * to action codes (ALU work with no memory dependence), the operands of group g + 1 are already
+ * in flight from the ring; its twist and store close the iteration.  A pass is four groups
+ * (896 words: one turn of the ring).  `sink` receives the codes:
+ *   sink.begin_pass(j)            before the first group of pass j (may wait for queue space)
+ *   sink.put(g, c0, c1, active)   codes of steps 56 g + lane and 56 g + 28 + lane
+ *   sink.end_pass(j)              after the last group of pass j (publishes progress)
+ * Lanes 28..31 shadow lane 27 (same loads, stores predicated off): no divergence. */
+template <typename Sink>
+__device__ __forceinline__ void gw_generate(uint32_t *ring, uint64_t groups, int lane, const ModConst &mrow,
+                                            const ModConst &mcol, uint32_t cols, Sink &sink) {
+    const bool active = lane < GW_ACTIVE;
+    const int l4 = 4 * (active ? lane : GW_ACTIVE - 1);
+    if (groups == 0) return;
+    GwOps o;
+    uint4 x0, x1;
+    gw_load<0>(ring, l4, o);
+    x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);
+    x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);
+    gw_store<0>(ring, l4, active, x0, x1);
+    __syncwarp();
+
+#define GW_BODY(PH, NEXT)                                                  \
+    {                                                                      \
+        if (NEXT) gw_load<((PH) + 1) & 3>(ring, l4, o);                    \
+        const uint32_t c0 = gw_code(x0, mrow, mcol, cols);                 \
+        const uint32_t c1 = gw_code(x1, mrow, mcol, cols);                 \
+        sink.put(g + (PH), c0, c1, active);                                \
+        if (NEXT) {                                                        \
+            x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);                      \
+            x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);                      \
+            gw_store<((PH) + 1) & 3>(ring, l4, active, x0, x1);            \
+            __syncwarp();                                                  \
+        }                                                                  \
+    }
+
+    uint64_t g = 0, pass = 0;
+    for (; g + 4 < groups; g += 4, ++pass) { /* every group of this pass has a successor */
+        sink.begin_pass(pass);
+        GW_BODY(0, true)
+        GW_BODY(1, true)
+        GW_BODY(2, true)
+        GW_BODY(3, true)
+        sink.end_pass(pass);
+    }
+    const uint32_t rest = (uint32_t)(groups - g); /* 1..4 groups left; (x0, x1) is group g, phase 0 */
+    sink.begin_pass(pass);
+    GW_BODY(0, rest > 1)
+    if (rest > 1) GW_BODY(1, rest > 2)
+    if (rest > 2) GW_BODY(2, rest > 3)
+    if (rest > 3) GW_BODY(3, false)
+    sink.end_pass(pass);
+#undef GW_BODY
 }
 
 /* ----------------------------------------------------------------- fused kernel */
@@ -101,7 +176,8 @@ struct Stream2Params {
     uint64_t chunk;   /* rollouts per stream */
     uint32_t streams; /* ceil(n / chunk) */
     uint32_t depth;   /* uniform depth_bound / max_depth */
-    uint32_t rb;      /* rollouts per queue buffer: 32 or 64 */
+    uint32_t rb;      /* rollouts per consumer batch */
+    uint32_t qlen;    /* codes per queue ring: power of two >= 2 * rb * depth + 448 */
     uint32_t cols, T, gen_words;
     ModConst mrow, mcol;
     const uint32_t *checkpoints; /* [streams][624] raw words preceding each stream's first model word */
@@ -127,116 +203,39 @@ struct RolloutAcc {
     unsigned long long w = 0, d = 0, l = 0, h = 0, n = 0;
 };
 
-/* One generator warp: `total_steps` model steps from its checkpoint into the code queue
- * [2][B].  Buffer k (absolute) uses half k & 1; barriers: full[half] = bar_base + half,
- * empty[half] = bar_base + 2 + half. */
+/* Code queue between a generator warp and its consumer: a ring of Q (power of two) codes
+ * indexed by absolute step number, plus two progress flags.  The generator may run at most
+ * Q codes ahead of what the consumer has released. */
 template <typename CodeT>
-__device__ __forceinline__ void gw_run(uint32_t *ring, CodeT *queue, uint32_t B, uint64_t total_steps, int bar_base,
-                                       const ModConst &mrow, const ModConst &mcol, uint32_t cols, int lane,
-                                       uint32_t *end_window) {
-    const int l4 = 4 * lane;
-    const bool active = lane < GW_ACTIVE;
-    const uint64_t groups = (total_steps + GW_STEPS - 1) / GW_STEPS;
-    const uint64_t nbuf = (total_steps + B - 1) / B; /* buffers the consumer will read */
-    uint32_t fill = 0, half = 0;
-    uint64_t buf = 0;      /* absolute index of the buffer being filled */
-    uint64_t produced = 0; /* steps emitted before the current group */
+struct QueueSink {
+    CodeT *queue;
+    uint32_t qmask;       /* Q - 1 */
+    uint32_t *prod_flag;  /* passes completed by the generator */
+    uint32_t *cons_flag;  /* codes released by the consumer, in units of `batch_codes` */
+    uint32_t batch_codes; /* rb * depth */
+    int lane;
+    uint32_t qpos = 0; /* (56 * g) & qmask for the next group */
 
-    auto emit = [&](uint32_t c0, uint32_t c1) {
-        /* entering a buffer for the first time: wait until the consumer has drained that half
-         * (buffers 0 and 1 start empty; nothing is waited for or written past the last buffer) */
-        if (fill == 0 && buf >= 2) nb_sync(bar_base + 2 + half);
-        if (fill + GW_STEPS > B && buf + 1 >= 2 && buf + 1 < nbuf) nb_sync(bar_base + 2 + (half ^ 1));
-        if (active) {
-            uint32_t i0 = fill + lane, i1 = fill + GW_ACTIVE + lane;
-            CodeT *q0 = queue + half * B, *q1 = q0;
-            if (i0 >= B) {
-                i0 -= B;
-                q0 = queue + (half ^ 1) * B;
-            }
-            if (i1 >= B) {
-                i1 -= B;
-                q1 = queue + (half ^ 1) * B;
-            }
-            if (produced + lane < total_steps) q0[i0] = (CodeT)c0;
-            if (produced + GW_ACTIVE + lane < total_steps) q1[i1] = (CodeT)c1;
-        }
-        fill += GW_STEPS;
-        produced += GW_STEPS;
-        if (fill >= B) {
-            nb_arrive(bar_base + half);
-            fill -= B;
-            half ^= 1;
-            ++buf;
-        }
-    };
-
-    uint64_t g = 0;
-    for (; g + 4 <= groups; g += 4) {
-        uint32_t c0 = 0, c1 = 0;
-        if (active) {
-            c0 = gw_step_code<0, 0>(ring, l4, mrow, mcol, cols);
-            c1 = gw_step_code<0, 1>(ring, l4, mrow, mcol, cols);
-        }
-        __syncwarp();
-        emit(c0, c1);
-        if (active) {
-            c0 = gw_step_code<1, 0>(ring, l4, mrow, mcol, cols);
-            c1 = gw_step_code<1, 1>(ring, l4, mrow, mcol, cols);
-        }
-        __syncwarp();
-        emit(c0, c1);
-        if (active) {
-            c0 = gw_step_code<2, 0>(ring, l4, mrow, mcol, cols);
-            c1 = gw_step_code<2, 1>(ring, l4, mrow, mcol, cols);
-        }
-        __syncwarp();
-        emit(c0, c1);
-        if (active) {
-            c0 = gw_step_code<3, 0>(ring, l4, mrow, mcol, cols);
-            c1 = gw_step_code<3, 1>(ring, l4, mrow, mcol, cols);
-        }
-        __syncwarp();
-        emit(c0, c1);
-    }
-    const uint32_t tail = (uint32_t)(groups - g); /* 0..3 groups in a last, partial pass */
-    if (tail > 0) {
-        uint32_t c0 = 0, c1 = 0;
-        if (active) {
-            c0 = gw_step_code<0, 0>(ring, l4, mrow, mcol, cols);
-            c1 = gw_step_code<0, 1>(ring, l4, mrow, mcol, cols);
-        }
-        __syncwarp();
-        emit(c0, c1);
-        if (tail > 1) {
-            if (active) {
-                c0 = gw_step_code<1, 0>(ring, l4, mrow, mcol, cols);
-                c1 = gw_step_code<1, 1>(ring, l4, mrow, mcol, cols);
-            }
-            __syncwarp();
-            emit(c0, c1);
-        }
-        if (tail > 2) {
-            if (active) {
-                c0 = gw_step_code<2, 0>(ring, l4, mrow, mcol, cols);
-                c1 = gw_step_code<2, 1>(ring, l4, mrow, mcol, cols);
-            }
-            __syncwarp();
-            emit(c0, c1);
+    __device__ __forceinline__ void begin_pass(uint64_t pass) {
+        /* this pass writes absolute codes [224 * pass, 224 * pass + 224): wait until they fit */
+        const uint64_t end = (pass + 1) * (uint64_t)GW_PASS_STEPS;
+        const uint64_t Q = (uint64_t)qmask + 1;
+        if (end > Q) {
+            while ((uint64_t)flag_acquire(cons_flag) * batch_codes + Q < end) __nanosleep(40);
         }
     }
-    /* a last, partly filled buffer; a group that overshot into a buffer beyond the last one the
-     * consumer will read leaves fill > 0 there, which is harmless */
-    if (fill > 0 && buf < nbuf) nb_arrive(bar_base + half);
-    if (end_window) {
-        /* words generated in the current pass before the stream's end: 4 * total_steps mod 896,
-         * except that a stream ending exactly on a pass boundary sits at 896 */
-        const uint64_t words = 4 * total_steps;
-        uint32_t w_end = (uint32_t)(words % GW_RING);
-        if (w_end == 0 && words > 0) w_end = GW_RING;
-        gw_dump_window(ring, w_end, end_window, lane);
+    __device__ __forceinline__ void put(uint64_t, uint32_t c0, uint32_t c1, bool active) {
+        if (active) {
+            queue[(qpos + lane) & qmask] = (CodeT)c0;
+            queue[(qpos + GW_ACTIVE + lane) & qmask] = (CodeT)c1;
+        }
+        qpos = (qpos + GW_STEPS) & qmask;
     }
-}
+    __device__ __forceinline__ void end_pass(uint64_t pass) {
+        __syncwarp();
+        if (lane == 0) flag_release(prod_flag, (uint32_t)(pass + 1));
+    }
+};
 
 /* Consumer side: the per-rollout walk over the shared state stream. */
 struct TreeWalk {
@@ -250,15 +249,18 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t d = P.depth;
     const uint32_t B = P.rb * d; /* codes per queue buffer */
-    /* layout: rings [PAIRS][896] u32 | fq doubles | queues [PAIRS][2][B] CodeT | table bytes */
+    /* layout: rings [PAIRS][896] u32 | flags [PAIRS][2] u32 (+pad) | fq doubles | queues [PAIRS][Q] CodeT | table */
     uint32_t *rings = reinterpret_cast<uint32_t *>(smem_raw);
-    double *sfq = reinterpret_cast<double *>(rings + GW_PAIRS * GW_RING);
+    uint32_t *flags = rings + GW_PAIRS * GW_RING;
+    double *sfq = reinterpret_cast<double *>(flags + 2 * GW_PAIRS);
     CodeT *queues = reinterpret_cast<CodeT *>(sfq + P.fq_len);
+    const uint32_t Q = P.qlen;
     const uint8_t *tab = P.tab;
+    if (tid < 2 * GW_PAIRS) flags[tid] = 0;
     if (KIND == KIND_TREE) {
         for (uint32_t i = tid; i < P.fq_len; i += blockDim.x) sfq[i] = P.fq[i];
         if (TAB_SMEM) {
-            uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * 2 * B);
+            uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * Q);
             stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
             for (uint32_t i = tid; i < P.tab_len; i += blockDim.x) stab[i] = P.tab[i];
             tab = stab;
@@ -268,7 +270,8 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const bool is_gen = warp < GW_PAIRS;
     const uint32_t stream = blockIdx.x * GW_PAIRS + pair;
     uint32_t *ring = rings + pair * GW_RING;
-    CodeT *queue = queues + (size_t)pair * 2 * B;
+    CodeT *queue = queues + (size_t)pair * Q;
+    uint32_t *prod_flag = flags + 2 * pair, *cons_flag = prod_flag + 1;
     if (stream < P.streams && is_gen) gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
     __syncthreads();
     if (stream >= P.streams) return;
@@ -276,13 +279,19 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const uint64_t first = (uint64_t)stream * P.chunk;
     const uint64_t cnt = (first + P.chunk <= P.n) ? P.chunk : P.n - first;
     const uint64_t total_steps = cnt * d;
-    /* four named barriers per pair: full[2], empty[2].  Id 0 doubles as __syncthreads, which is
-     * only used above, before any pair starts. */
-    const int bar_base = 4 * pair;
+    const uint32_t qmask = Q - 1;
 
     if (is_gen) {
-        uint32_t *endw = (stream + 1 == P.streams) ? P.end_window : nullptr;
-        gw_run<CodeT>(ring, queue, B, total_steps, bar_base, P.mrow, P.mcol, P.cols, lane, endw);
+        QueueSink<CodeT> sink{queue, qmask, prod_flag, cons_flag, B, lane};
+        gw_generate(ring, (total_steps + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
+        if (stream + 1 == P.streams && P.end_window) {
+            /* words generated in the current pass before the stream's end: 4 * total_steps mod 896,
+             * except that a stream ending exactly on a pass boundary sits at 896 */
+            const uint64_t words = 4 * total_steps;
+            uint32_t w_end = (uint32_t)(words % GW_RING);
+            if (w_end == 0 && words > 0) w_end = GW_RING;
+            gw_dump_window(ring, w_end, P.end_window, lane);
+        }
         return;
     }
 
@@ -291,20 +300,25 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const uint64_t nbuf = (cnt + P.rb - 1) / P.rb;
     const uint32_t T = P.T;
     for (uint64_t k = 0; k < nbuf; ++k) {
-        const uint32_t half = (uint32_t)(k & 1);
-        nb_sync(bar_base + half);
-        const CodeT *buf = queue + half * B;
         const uint64_t r0 = k * P.rb;
         const uint32_t live = (uint32_t)((cnt - r0 < P.rb) ? cnt - r0 : P.rb);
+        {
+            /* codes of rollouts r0 .. r0 + live - 1 are complete once the generator has finished
+             * the pass containing step (r0 + live) * d - 1 */
+            const uint64_t need = ((r0 + live) * d + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
+            while ((uint64_t)flag_acquire(prod_flag) < need) __nanosleep(100);
+        }
+        const uint32_t kbase = (uint32_t)((r0 * d) & qmask);
         for (uint32_t r = lane; r < live; r += 32) {
             const uint64_t i = first + r0 + r;
-            const CodeT *my = buf + (size_t)r * d;
+            const uint32_t qb = kbase + r * d;
+#define MY_CODE(s_) ((uint32_t)queue[(qb + (s_)) & qmask])
             uint32_t h = PCU_HASH_INIT;
             uint32_t pay = 0;
             uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
             if (KIND == KIND_MOLD) {
                 for (uint32_t s = 0; s < d; ++s) {
-                    const uint32_t code = my[s];
+                    const uint32_t code = MY_CODE(s);
                     h = hash_step(h, code, 0);
                     if (tr) {
                         const uint32_t rr = code / P.cols;
@@ -320,7 +334,7 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
                 if (T == 1) {
                     const uint32_t adv = 2 + P.gen_words;
                     for (uint32_t s = 0; s < d; ++s) {
-                        const uint32_t code = my[s];
+                        const uint32_t code = MY_CODE(s);
                         p += code; /* discard(row*cols + col): random-tree.hh:88-89 */
                         bias += (int)((tab[p] >> 4) & 3u) - 1;
                         p += adv;
@@ -335,7 +349,7 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
                 } else {
                     uint32_t gb = p - P.gen_words; /* where the current chance strategies were drawn */
                     for (uint32_t s = 0; s < d; ++s) {
-                        const uint32_t code = my[s];
+                        const uint32_t code = MY_CODE(s);
                         const uint32_t st = code * T;
                         const uint8_t *cell = tab + gb + 2 * st;
                         int S = 0;
@@ -384,8 +398,9 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
             acc.h += h;
             acc.n += 1;
         }
+#undef MY_CODE
         __syncwarp();
-        if (k + 2 < nbuf) nb_arrive(bar_base + 2 + half);
+        if (lane == 0) flag_release(cons_flag, (uint32_t)(k + 1));
     }
     if (P.sums) {
         acc.w = warp_sum_u64(acc.w);
@@ -419,6 +434,20 @@ struct Gen2Params {
 };
 
 template <typename CodeT>
+struct GlobalSink {
+    CodeT *codes; /* first code of this stream */
+    uint64_t count;
+    int lane;
+    __device__ __forceinline__ void begin_pass(uint64_t) {}
+    __device__ __forceinline__ void put(uint64_t g, uint32_t c0, uint32_t c1, bool active) {
+        const uint64_t q = g * GW_STEPS + lane;
+        if (active && q < count) codes[q] = (CodeT)c0;
+        if (active && q + GW_ACTIVE < count) codes[q + GW_ACTIVE] = (CodeT)c1;
+    }
+    __device__ __forceinline__ void end_pass(uint64_t) {}
+};
+
+template <typename CodeT>
 __global__ void __launch_bounds__(128) k_gen_codes2(const Gen2Params P) {
     __shared__ __align__(16) uint32_t rings[4 * GW_RING];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -429,31 +458,8 @@ __global__ void __launch_bounds__(128) k_gen_codes2(const Gen2Params P) {
     const uint64_t last = (first + P.chunk_steps < P.total_steps) ? first + P.chunk_steps : P.total_steps;
     gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
     __syncwarp();
-    CodeT *codes = reinterpret_cast<CodeT *>(P.codes);
-    const int l4 = 4 * lane;
-    const bool active = lane < GW_ACTIVE;
-    uint64_t q = first;
-#define GEN2_GROUP(PH)                                                              \
-    {                                                                               \
-        if (active) {                                                               \
-            const uint32_t c0 = gw_step_code<PH, 0>(ring, l4, P.mrow, P.mcol, P.cols); \
-            const uint32_t c1 = gw_step_code<PH, 1>(ring, l4, P.mrow, P.mcol, P.cols); \
-            if (q + lane < last) codes[q + lane] = (CodeT)c0;                       \
-            if (q + GW_ACTIVE + lane < last) codes[q + GW_ACTIVE + lane] = (CodeT)c1; \
-        }                                                                           \
-        __syncwarp();                                                               \
-        q += GW_STEPS;                                                              \
-    }
-    while (q < last) {
-        GEN2_GROUP(0)
-        if (q >= last) break;
-        GEN2_GROUP(1)
-        if (q >= last) break;
-        GEN2_GROUP(2)
-        if (q >= last) break;
-        GEN2_GROUP(3)
-    }
-#undef GEN2_GROUP
+    GlobalSink<CodeT> sink{reinterpret_cast<CodeT *>(P.codes) + first, last - first, lane};
+    gw_generate(ring, (last - first + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
     if (stream + 1 == P.streams && P.end_window) {
         const uint64_t words = 4 * (last - first);
         uint32_t w_end = (uint32_t)(words % GW_RING);
