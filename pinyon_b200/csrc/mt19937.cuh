@@ -62,6 +62,48 @@ __device__ __forceinline__ uint32_t mod64(uint32_t hi, uint32_t lo, const ModCon
     const uint32_t b = mod32(lo, c.n, c.m);
     return mod32(a * c.c32 + b, c.n, c.m);
 }
+/* The same twist written for the B200 pipes (LOP3/SHF on the ALU pipe at 64 lanes/clk/SM,
+ * IMAD on the FMA pipe at 64 more): one bit-select LOP3, one shift, (b & 1) * matrix as
+ * LOP3 + IMAD, one three-way XOR -> 4 ALU + 1 FMA instructions instead of 6 + 1. */
+__device__ __forceinline__ uint32_t mt_twist_dev(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t y, x;
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(y) : "r"(a), "r"(b), "r"(0x80000000u)); /* (a & m) | (b & ~m) */
+    uint32_t mag; /* written as a multiply-add so that it issues on the FMA pipe */
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(mag) : "r"(b & 1u), "r"(0x9908b0dfu), "r"(0u));
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(x) : "r"(c), "r"(y >> 1), "r"(mag));
+    return x;
+}
+
+/* Per-modulus constants of the folded 64-bit reduction below (n <= 256). */
+struct FoldConst {
+    uint32_t n, m, c32, k1, k2; /* m = floor(2^32 / n); see mod64_fold */
+};
+
+inline FoldConst make_fold_const(uint32_t n) {
+    FoldConst f;
+    const uint32_t c16 = (n <= 1) ? 0u : (uint32_t)(0x10000ull % n);
+    const uint32_t c48 = (n <= 1) ? 0u : (uint32_t)(0x1000000000000ull % n);
+    f.n = n;
+    f.m = (n <= 1) ? 0xffffffffu : (uint32_t)(0x100000000ull / n);
+    f.c32 = (n <= 1) ? 0u : (uint32_t)(0x100000000ull % n);
+    f.k1 = c48 - 65536u * f.c32; /* mod 2^32 */
+    f.k2 = c16 - 65536u;
+    return f;
+}
+
+/* (hi:lo) mod n == prng::random_int(n) (random.hh:26,28) for n <= 256, with ONE high multiply:
+ * with ck = 2^k mod n the four 16-bit digits fold to
+ *   s = (hi >> 16) c48 + (hi & 0xffff) c32 + (lo >> 16) c16 + (lo & 0xffff)  < 65535 (3 * 255 + 1) < 2^26,
+ * evaluated in wrapping 32-bit arithmetic as (hi >> 16) k1 + hi c32 + (lo >> 16) k2 + lo with
+ * k1 = c48 - 2^16 c32, k2 = c16 - 2^16 (two shifts on the ALU pipe, three IMADs on the FMA pipe),
+ * and s is reduced once.  IMAD.HI issues at less than half the IMAD rate on sm_100 (measured:
+ * 28 vs 64 lanes/clk/SM) and stalls the ALU pipe while it does, so the three of them in the
+ * word-by-word reduction (mod64) were the most expensive part of a model step. */
+__device__ __forceinline__ uint32_t mod64_fold(uint32_t hi, uint32_t lo, const FoldConst &f) {
+    const uint32_t s = (hi >> 16) * f.k1 + hi * f.c32 + (lo >> 16) * f.k2 + lo;
+    return mod32(s, f.n, f.m);
+}
+
 /* prng::uniform() (random.hh:23): generate_canonical<double,53> over a 32-bit engine;
  * first draw is the LOW word; one rounding (in the add); clamp below 1. */
 __device__ __forceinline__ double prng_uniform_from_words(uint32_t first, uint32_t second) {

@@ -382,7 +382,7 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.traj_hash = od.hash;
     P.sums = od.sums;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
-    const size_t queue_bytes = (size_t)GW_PAIRS * P.qlen * (code8 ? 1 : 2);
+    const size_t queue_bytes = (size_t)GW_PAIRS * (P.qlen + 16) * (code8 ? 1 : 2);
     size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + 2 * GW_PAIRS * 4 + (size_t)P.fq_len * 8 + queue_bytes + 16;
     bool tab_smem = false;
     if (KIND == KIND_TREE && smem + P.tab_len + 16 <= SMEM_LIMIT) {
@@ -414,8 +414,8 @@ int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, 
     G.chunk_steps = chunk;
     G.streams = (uint32_t)streams;
     G.cols = cols;
-    G.mrow = make_mod_const(rows);
-    G.mcol = make_mod_const(cols);
+    G.mrow = make_fold_const(rows);
+    G.mcol = make_fold_const(cols);
     G.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
     G.codes = ctx->buf[B_CODES].p;
     G.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
@@ -762,8 +762,8 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         P.cols = b->cols;
         P.T = T;
         P.gen_words = gen_words;
-        P.mrow = make_mod_const(b->rows);
-        P.mcol = make_mod_const(b->cols);
+        P.mrow = make_fold_const(b->rows);
+        P.mcol = make_fold_const(b->cols);
         P.tab = reinterpret_cast<const uint8_t *>(ctx->buf[B_TAB].p);
         P.tab_base = tab_base;
         P.tab_len = tab_len;
@@ -858,8 +858,8 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         P.depth = b->depth_u;
         P.cols = b->n_actions;
         P.T = 1;
-        P.mrow = make_mod_const(b->n_actions);
-        P.mcol = make_mod_const(b->n_actions);
+        P.mrow = make_fold_const(b->n_actions);
+        P.mcol = make_fold_const(b->n_actions);
         P.traj_stride = out->traj_stride;
         ctx->path = "stream_mold";
         if ((rc = run_stream<KIND_MOLD>(ctx, P, b->n_actions, rng, od))) return rc;

@@ -70,10 +70,10 @@ __device__ __forceinline__ void gw_load(const uint32_t *ring, int l4, GwOps &o) 
 
 __device__ __forceinline__ uint4 gw_twist4(const uint4 &a, uint32_t a4, const uint4 &c, uint32_t c4) {
     uint4 x;
-    x.x = mt_twist(a.x, a.y, c.y);
-    x.y = mt_twist(a.y, a.z, c.z);
-    x.z = mt_twist(a.z, a.w, c.w);
-    x.w = mt_twist(a.w, a4, c4);
+    x.x = mt_twist_dev(a.x, a.y, c.y);
+    x.y = mt_twist_dev(a.y, a.z, c.z);
+    x.z = mt_twist_dev(a.z, a.w, c.w);
+    x.w = mt_twist_dev(a.w, a4, c4);
     return x;
 }
 
@@ -88,9 +88,9 @@ __device__ __forceinline__ void gw_store(uint32_t *ring, int l4, bool active, co
 
 /* Raw words of one step -> joint action code row * cols + col: temper, then the two
  * random_int draws (uniform_64 takes the HIGH word first, random.hh:26,28). */
-__device__ __forceinline__ uint32_t gw_code(const uint4 &x, const ModConst &mrow, const ModConst &mcol, uint32_t cols) {
-    const uint32_t row = mod64(mt_temper(x.x), mt_temper(x.y), mrow);
-    const uint32_t col = mod64(mt_temper(x.z), mt_temper(x.w), mcol);
+__device__ __forceinline__ uint32_t gw_code(const uint4 &x, const FoldConst &mrow, const FoldConst &mcol, uint32_t cols) {
+    const uint32_t row = mod64_fold(mt_temper(x.x), mt_temper(x.y), mrow);
+    const uint32_t col = mod64_fold(mt_temper(x.z), mt_temper(x.w), mcol);
     return row * cols + col;
 }
 
@@ -103,15 +103,12 @@ __device__ __forceinline__ void gw_dump_window(const uint32_t *ring, uint32_t w_
     for (int i = lane; i < MT_N; i += 32) dst[i] = ring[(w_end + 48 + i) % GW_RING];
 }
 
-/* Shared-memory flags between a generator warp and its consumer warp. */
-__device__ __forceinline__ void flag_release(uint32_t *flag, uint32_t v) {
-    asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(flag)), "r"(v)
-                 : "memory");
-}
-__device__ __forceinline__ uint32_t flag_acquire(const uint32_t *flag) {
-    uint32_t v;
-    asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"((uint32_t)__cvta_generic_to_shared(flag)) : "memory");
-    return v;
+/* Named barriers between a generator warp and its consumer warp (64 threads each): a waiting
+ * warp takes no issue slots, unlike a polling loop on the same scheduler. */
+__device__ __forceinline__ void nb_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void nb_arrive(int id) {
+    __threadfence_block();
+    asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
 }
 
 /* The generator loop, software pipelined: while the 8 words of group g are tempered and reduced
@@ -123,8 +120,8 @@ __device__ __forceinline__ uint32_t flag_acquire(const uint32_t *flag) {
  *   sink.end_pass(j)              after the last group of pass j (publishes progress)
  * Lanes 28..31 shadow lane 27 (same loads, stores predicated off): no divergence. */
 template <typename Sink>
-__device__ __forceinline__ void gw_generate(uint32_t *ring, uint64_t groups, int lane, const ModConst &mrow,
-                                            const ModConst &mcol, uint32_t cols, Sink &sink) {
+__device__ __forceinline__ void gw_generate(uint32_t *ring, uint64_t groups, int lane, const FoldConst &mrow,
+                                            const FoldConst &mcol, uint32_t cols, Sink &sink) {
     const bool active = lane < GW_ACTIVE;
     const int l4 = 4 * (active ? lane : GW_ACTIVE - 1);
     if (groups == 0) return;
@@ -179,7 +176,7 @@ struct Stream2Params {
     uint32_t rb;      /* rollouts per consumer batch */
     uint32_t qlen;    /* codes per queue ring: power of two >= 2 * rb * depth + 448 */
     uint32_t cols, T, gen_words;
-    ModConst mrow, mcol;
+    FoldConst mrow, mcol;
     const uint32_t *checkpoints; /* [streams][624] raw words preceding each stream's first model word */
     const uint8_t *tab;          /* state-stream table: low nibble u64%10, bits 4-5 u64%3 at each draw index */
     uint32_t tab_base, tab_len;
@@ -204,36 +201,32 @@ struct RolloutAcc {
 };
 
 /* Code queue between a generator warp and its consumer: a ring of Q (power of two) codes
- * indexed by absolute step number, plus two progress flags.  The generator may run at most
- * Q codes ahead of what the consumer has released. */
+ * indexed by absolute step number.  Hand-off is per pass (224 codes) over four named barriers,
+ * full[2] = bar + {0,1} and empty[2] = bar + {2,3}, indexed by pass parity: the generator
+ * arrives on full[j & 1] after pass j and, from pass 2 on, first waits on empty[j & 1], which the
+ * consumer arrives on once it has played every rollout completed by pass j - 2.  Unplayed codes
+ * are then less than one batch plus two passes: Q >= 2 * rb * depth + 448 holds them. */
 template <typename CodeT>
 struct QueueSink {
-    CodeT *queue;
-    uint32_t qmask;       /* Q - 1 */
-    uint32_t *prod_flag;  /* passes completed by the generator */
-    uint32_t *cons_flag;  /* codes released by the consumer, in units of `batch_codes` */
-    uint32_t batch_codes; /* rb * depth */
+    CodeT *queue; /* Q codes, then a dummy slot for the shadow lanes */
+    uint32_t qmask;
+    int bar;
     int lane;
     uint32_t qpos = 0; /* (56 * g) & qmask for the next group */
 
     __device__ __forceinline__ void begin_pass(uint64_t pass) {
-        /* this pass writes absolute codes [224 * pass, 224 * pass + 224): wait until they fit */
-        const uint64_t end = (pass + 1) * (uint64_t)GW_PASS_STEPS;
-        const uint64_t Q = (uint64_t)qmask + 1;
-        if (end > Q) {
-            while ((uint64_t)flag_acquire(cons_flag) * batch_codes + Q < end) __nanosleep(40);
-        }
+        if (pass >= 2) nb_sync(bar + 2 + (int)(pass & 1));
     }
     __device__ __forceinline__ void put(uint64_t, uint32_t c0, uint32_t c1, bool active) {
-        if (active) {
-            queue[(qpos + lane) & qmask] = (CodeT)c0;
-            queue[(qpos + GW_ACTIVE + lane) & qmask] = (CodeT)c1;
-        }
+        const uint32_t i0 = active ? ((qpos + lane) & qmask) : qmask + 1;
+        const uint32_t i1 = active ? ((qpos + GW_ACTIVE + lane) & qmask) : qmask + 1;
+        queue[i0] = (CodeT)c0;
+        queue[i1] = (CodeT)c1;
         qpos = (qpos + GW_STEPS) & qmask;
     }
     __device__ __forceinline__ void end_pass(uint64_t pass) {
         __syncwarp();
-        if (lane == 0) flag_release(prod_flag, (uint32_t)(pass + 1));
+        nb_arrive(bar + (int)(pass & 1));
     }
 };
 
@@ -249,18 +242,16 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t d = P.depth;
     const uint32_t B = P.rb * d; /* codes per queue buffer */
-    /* layout: rings [PAIRS][896] u32 | flags [PAIRS][2] u32 (+pad) | fq doubles | queues [PAIRS][Q] CodeT | table */
+    /* layout: rings [PAIRS][896] u32 | fq doubles | queues [PAIRS][Q + 16] CodeT | table */
     uint32_t *rings = reinterpret_cast<uint32_t *>(smem_raw);
-    uint32_t *flags = rings + GW_PAIRS * GW_RING;
-    double *sfq = reinterpret_cast<double *>(flags + 2 * GW_PAIRS);
+    double *sfq = reinterpret_cast<double *>(rings + GW_PAIRS * GW_RING);
     CodeT *queues = reinterpret_cast<CodeT *>(sfq + P.fq_len);
     const uint32_t Q = P.qlen;
     const uint8_t *tab = P.tab;
-    if (tid < 2 * GW_PAIRS) flags[tid] = 0;
     if (KIND == KIND_TREE) {
         for (uint32_t i = tid; i < P.fq_len; i += blockDim.x) sfq[i] = P.fq[i];
         if (TAB_SMEM) {
-            uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * Q);
+            uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * (Q + 16));
             stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
             for (uint32_t i = tid; i < P.tab_len; i += blockDim.x) stab[i] = P.tab[i];
             tab = stab;
@@ -270,8 +261,10 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const bool is_gen = warp < GW_PAIRS;
     const uint32_t stream = blockIdx.x * GW_PAIRS + pair;
     uint32_t *ring = rings + pair * GW_RING;
-    CodeT *queue = queues + (size_t)pair * Q;
-    uint32_t *prod_flag = flags + 2 * pair, *cons_flag = prod_flag + 1;
+    CodeT *queue = queues + (size_t)pair * (Q + 16);
+    /* four named barriers per pair; id 0 doubles as __syncthreads, used only below, before any
+     * pair starts */
+    const int bar = 4 * pair;
     if (stream < P.streams && is_gen) gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
     __syncthreads();
     if (stream >= P.streams) return;
@@ -282,7 +275,7 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const uint32_t qmask = Q - 1;
 
     if (is_gen) {
-        QueueSink<CodeT> sink{queue, qmask, prod_flag, cons_flag, B, lane};
+        QueueSink<CodeT> sink{queue, qmask, bar, lane};
         gw_generate(ring, (total_steps + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
         if (stream + 1 == P.streams && P.end_window) {
             /* words generated in the current pass before the stream's end: 4 * total_steps mod 896,
@@ -299,15 +292,15 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     RolloutAcc acc;
     const uint64_t nbuf = (cnt + P.rb - 1) / P.rb;
     const uint32_t T = P.T;
-    for (uint64_t k = 0; k < nbuf; ++k) {
+    const uint64_t npass = (total_steps + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
+    uint64_t k = 0; /* next batch of rb rollouts */
+    for (uint64_t j = 0; j < npass; ++j) {
+      nb_sync(bar + (int)(j & 1));
+      const uint64_t avail = ((j + 1) * GW_PASS_STEPS < total_steps) ? (j + 1) * GW_PASS_STEPS : total_steps;
+      for (; k < nbuf; ++k) { /* every batch whose codes pass j completed */
         const uint64_t r0 = k * P.rb;
         const uint32_t live = (uint32_t)((cnt - r0 < P.rb) ? cnt - r0 : P.rb);
-        {
-            /* codes of rollouts r0 .. r0 + live - 1 are complete once the generator has finished
-             * the pass containing step (r0 + live) * d - 1 */
-            const uint64_t need = ((r0 + live) * d + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
-            while ((uint64_t)flag_acquire(prod_flag) < need) __nanosleep(100);
-        }
+        if ((r0 + live) * d > avail) break;
         const uint32_t kbase = (uint32_t)((r0 * d) & qmask);
         for (uint32_t r = lane; r < live; r += 32) {
             const uint64_t i = first + r0 + r;
@@ -399,8 +392,11 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
             acc.n += 1;
         }
 #undef MY_CODE
-        __syncwarp();
-        if (lane == 0) flag_release(cons_flag, (uint32_t)(k + 1));
+      }
+      if (j + 2 < npass) {
+          __syncwarp();
+          nb_arrive(bar + 2 + (int)(j & 1));
+      }
     }
     if (P.sums) {
         acc.w = warp_sum_u64(acc.w);
@@ -427,7 +423,7 @@ struct Gen2Params {
     uint64_t chunk_steps; /* steps per stream */
     uint32_t streams;
     uint32_t cols;
-    ModConst mrow, mcol;
+    FoldConst mrow, mcol;
     const uint32_t *checkpoints;
     void *codes; /* CodeT[total_steps] */
     uint32_t *end_window;
