@@ -67,7 +67,9 @@ struct pcu_ctx {
     struct {
         bool valid = false;
         uint64_t seed = 0;
-        uint32_t base = 0, len = 0;
+        uint32_t base = 0, len = 0, T = 0;
+        double pu = 0;
+        int32_t thr_p = 0, thr_q = 1;
     } tab_key;
     /* cached fq table */
     uint32_t fq_w = 0;
@@ -157,24 +159,64 @@ void host_window_advance(uint32_t *win, uint64_t words) {
 
 /* ------------------------------------------------------- state-stream table */
 
-/* tab[j] describes draw index base + j of prng{seed}: low nibble = u64 % 10, bits
- * 4-5 = u64 % 3, where u64 = (draw[j] << 32) | draw[j+1] (random.hh:26,28). */
-void host_build_table(uint64_t seed, uint32_t base, uint32_t len, std::vector<uint8_t> &tab) {
+void host_build_fq(uint32_t T, std::vector<double> &fq, uint32_t *w_out);
+
+/* Two byte tables over draw indices base .. base + len - 1 of prng{seed}, with
+ * u64_j = (draw[j] << 32) | draw[j+1] (random.hh:26,28):
+ *   tab[j]         = u64_j % 3 - 1 as int8: the payoff-bias step drawn at j (random-tree.hh:97)
+ *   tab[len + j]   (T > 1) the chance action apply_actions(row, col) picks (random-tree.hh:115-135)
+ *                  for a cell whose T strategy draws start at j: n_k = u64_{j+2k} % 10 + 1,
+ *                  thresholded and normalised as get_chance_strategies does (:154-199), then the
+ *                  reference's own double arithmetic p -= (double)(float)(n_k / S) from
+ *                  p = prng{transition_seed}.uniform().  One entry per POSITION, so a rollout
+ *                  step is two table reads whatever T is. */
+void host_build_table(uint64_t seed, uint32_t base, uint32_t len, uint32_t T, double pu, int thr_p, int thr_q,
+                      std::vector<uint8_t> &tab) {
     std::vector<uint32_t> x(MT_N);
     uint32_t p;
     host_mt_seed(seed, x.data(), &p);
-    const uint64_t need = (uint64_t)base + len + 1;
-    std::vector<uint32_t> w(len + 1);
+    const uint32_t extra = 2 * T + 2;
+    const uint64_t need = (uint64_t)base + len + extra;
+    std::vector<uint32_t> w(len + extra);
     uint64_t idx = 0;
     while (idx < need) {
         host_mt_refill(x.data());
         for (uint32_t k = 0; k < MT_N && idx < need; ++k, ++idx)
             if (idx >= base) w[idx - base] = mt_temper(x[k]);
     }
-    tab.resize(len);
-    for (uint32_t j = 0; j < len; ++j) {
+    tab.assign((size_t)len * (T > 1 ? 2 : 1), 0);
+    std::vector<uint8_t> n10(len + extra - 1);
+    for (uint32_t j = 0; j + 1 < len + extra; ++j) {
         const uint64_t u = ((uint64_t)w[j] << 32) | w[j + 1];
-        tab[j] = (uint8_t)((u % 10) | ((u % 3) << 4));
+        n10[j] = (uint8_t)(u % 10);
+        if (j < len) tab[j] = (uint8_t)(int8_t)((int)(u % 3) - 1);
+    }
+    if (T > 1) {
+        std::vector<double> fq;
+        uint32_t fw;
+        host_build_fq(T, fq, &fw);
+        for (uint32_t j = 0; j < len; ++j) {
+            int nk[9], S = 0;
+            for (uint32_t k = 0; k < T; ++k) {
+                nk[k] = (int)n10[j + 2 * k] + 1;
+                if (nk[k] * thr_q < thr_p * 10) nk[k] = 0;
+                S += nk[k];
+            }
+            if (S == 0) {
+                nk[0] = 1;
+                S = 1;
+            }
+            volatile double pp = pu;
+            uint32_t ch = 0;
+            for (uint32_t k = 0; k < T; ++k) {
+                pp = pp - fq[(size_t)nk[k] * fw + S];
+                if (pp <= 0) {
+                    ch = k;
+                    break;
+                }
+            }
+            tab[(size_t)len + j] = (uint8_t)ch;
+        }
     }
 }
 
@@ -383,11 +425,12 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.sums = od.sums;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
     const size_t queue_bytes = (size_t)GW_PAIRS * (P.qlen + 16) * (code8 ? 1 : 2);
-    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + 2 * GW_PAIRS * 4 + (size_t)P.fq_len * 8 + queue_bytes + 16;
+    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + queue_bytes + 16;
+    const size_t tab_bytes = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
     bool tab_smem = false;
-    if (KIND == KIND_TREE && smem + P.tab_len + 16 <= SMEM_LIMIT) {
+    if (KIND == KIND_TREE && smem + tab_bytes + 16 <= SMEM_LIMIT) {
         tab_smem = true;
-        smem += P.tab_len + 16;
+        smem += tab_bytes + 16;
     }
     if (smem > SMEM_LIMIT) return fail(ctx, PCU_ERR_UNSUPPORTED, "depth %u needs %zu B of shared memory", P.depth, smem);
     if (code8)
@@ -743,17 +786,23 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     if (fused) {
         const uint32_t tab_base = pos_min - gen_words;
         const uint32_t tab_len = (uint32_t)span;
-        if (!(ctx->tab_key.valid && ctx->tab_key.seed == (uint32_t)b->state_seed_u && ctx->tab_key.base == tab_base &&
-              ctx->tab_key.len >= tab_len)) {
+        const double pu = (T > 1) ? host_uniform_from_seed(b->transition_seed_u) : 0.0;
+        auto &key = ctx->tab_key;
+        if (!(key.valid && key.seed == (uint32_t)b->state_seed_u && key.base == tab_base && key.len == tab_len &&
+              key.T == T && key.pu == pu && key.thr_p == b->thr_p && key.thr_q == b->thr_q)) {
             std::vector<uint8_t> tab;
-            host_build_table(b->state_seed_u, tab_base, tab_len, tab);
-            CU(ctx->buf[B_TAB].ensure(tab_len));
-            CU(cudaMemcpyAsync(ctx->buf[B_TAB].p, tab.data(), tab_len, cudaMemcpyHostToDevice, ctx->stream));
+            host_build_table(b->state_seed_u, tab_base, tab_len, T, pu, b->thr_p, b->thr_q, tab);
+            CU(ctx->buf[B_TAB].ensure(tab.size()));
+            CU(cudaMemcpyAsync(ctx->buf[B_TAB].p, tab.data(), tab.size(), cudaMemcpyHostToDevice, ctx->stream));
             CU(cudaStreamSynchronize(ctx->stream));
-            ctx->tab_key.valid = true;
-            ctx->tab_key.seed = (uint32_t)b->state_seed_u;
-            ctx->tab_key.base = tab_base;
-            ctx->tab_key.len = tab_len;
+            key.valid = true;
+            key.seed = (uint32_t)b->state_seed_u;
+            key.base = tab_base;
+            key.len = tab_len;
+            key.T = T;
+            key.pu = pu;
+            key.thr_p = b->thr_p;
+            key.thr_q = b->thr_q;
         }
         Stream2Params P;
         memset(&P, 0, sizeof(P));
@@ -771,12 +820,6 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         P.state_pos_u = b->state_pos_u;
         P.bias = d_bias;
         P.bias_u = b->payoff_bias_u;
-        P.pu = (T > 1) ? host_uniform_from_seed(b->transition_seed_u) : 0.0;
-        P.thr_p = b->thr_p;
-        P.thr_q = b->thr_q;
-        P.fq = d_fq;
-        P.fq_w = fq_w;
-        P.fq_len = (T > 1) ? 11u * fq_w : 0u;
         P.traj_stride = out->traj_stride;
         ctx->path = "stream_table";
         if ((rc = run_stream<KIND_TREE>(ctx, P, b->rows, rng, od))) return rc;

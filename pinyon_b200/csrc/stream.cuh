@@ -178,16 +178,13 @@ struct Stream2Params {
     uint32_t cols, T, gen_words;
     FoldConst mrow, mcol;
     const uint32_t *checkpoints; /* [streams][624] raw words preceding each stream's first model word */
-    const uint8_t *tab;          /* state-stream table: low nibble u64%10, bits 4-5 u64%3 at each draw index */
+    const uint8_t *tab;          /* [tab_len] int8 bias steps, then (T > 1) [tab_len] chance actions; see
+                                    host_build_table */
     uint32_t tab_base, tab_len;
     const uint32_t *state_pos;
     uint32_t state_pos_u;
     const int32_t *bias;
     int32_t bias_u;
-    double pu;
-    int32_t thr_p, thr_q;
-    const double *fq; /* fq[n * fq_w + S] = (double)(float)(n / (double)S) */
-    uint32_t fq_w, fq_len;
     uint8_t *payoff;
     uint8_t *traj;
     uint32_t traj_stride;
@@ -230,11 +227,74 @@ struct QueueSink {
     }
 };
 
-/* Consumer side: the per-rollout walk over the shared state stream. */
-struct TreeWalk {
-    uint32_t p, gb, h;
-    int bias;
-};
+/* Consumer side: one rollout = `d` codes of the queue walked over the shared state stream.
+ * Codes of a rollout are contiguous in the ring (index & qmask).  All return the trajectory
+ * hash; TRAJ also writes (row, col, chance) bytes. */
+template <bool TRAJ>
+__device__ __forceinline__ void put_traj(uint8_t *tr, uint32_t s, uint32_t code, uint32_t cols, uint32_t ch) {
+    if (TRAJ) {
+        const uint32_t rr = code / cols;
+        tr[3 * s + 0] = (uint8_t)rr;
+        tr[3 * s + 1] = (uint8_t)(code - rr * cols);
+        tr[3 * s + 2] = (uint8_t)ch;
+    }
+}
+
+template <bool TRAJ, typename CodeT>
+__device__ __forceinline__ uint32_t walk_mold(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
+                                              uint8_t *tr) {
+    uint32_t h = PCU_HASH_INIT;
+#pragma unroll 2
+    for (uint32_t s = 0; s < d; ++s) {
+        const uint32_t code = queue[(qb + s) & qmask];
+        h = hash_step(h, code, 0);
+        put_traj<TRAJ>(tr, s, code, cols, 0);
+    }
+    return h;
+}
+
+/* T == 1: chance strategies are all 1, chance action 0 (random-tree.hh:115-135 with p - 1 <= 0);
+ * a step is discard(row * cols + col), one bias draw, then 2 * rows * cols strategy draws. */
+template <bool TRAJ, typename CodeT>
+__device__ __forceinline__ uint32_t walk_tree1(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
+                                               const int8_t *tb, uint32_t p, uint32_t adv, int &bias, uint8_t *tr) {
+    uint32_t h = PCU_HASH_INIT;
+    int b = bias;
+#pragma unroll 2
+    for (uint32_t s = 0; s < d; ++s) {
+        const uint32_t code = queue[(qb + s) & qmask];
+        const uint32_t t = p + code; /* discard(row*cols + col): random-tree.hh:88-89 */
+        b += tb[t];
+        p = t + adv;
+        h = hash_step(h, code, 0);
+        put_traj<TRAJ>(tr, s, code, cols, 0);
+    }
+    bias = b;
+    return h;
+}
+
+/* T > 1: the chance action of the chosen cell comes from the per-position table. */
+template <bool TRAJ, typename CodeT>
+__device__ __forceinline__ uint32_t walk_treeT(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
+                                               uint32_t T, const int8_t *tb, const uint8_t *tch, uint32_t p,
+                                               uint32_t gen_words, int &bias, uint8_t *tr) {
+    uint32_t h = PCU_HASH_INIT;
+    int b = bias;
+    uint32_t gb = p - gen_words; /* where the current chance strategies were drawn */
+#pragma unroll 2
+    for (uint32_t s = 0; s < d; ++s) {
+        const uint32_t code = queue[(qb + s) & qmask];
+        const uint32_t st = code * T;
+        const uint32_t ch = tch[gb + 2 * st];
+        const uint32_t t = gb + gen_words + st + ch; /* discard(get_transition_idx): random-tree.hh:88-89,149-152 */
+        b += tb[t];
+        gb = t + 2;
+        h = hash_step(h, code, ch);
+        put_traj<TRAJ>(tr, s, code, cols, ch);
+    }
+    bias = b;
+    return h;
+}
 
 template <int KIND, typename CodeT, bool TAB_SMEM>
 __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P) {
@@ -242,20 +302,17 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t d = P.depth;
     const uint32_t B = P.rb * d; /* codes per queue buffer */
-    /* layout: rings [PAIRS][896] u32 | fq doubles | queues [PAIRS][Q + 16] CodeT | table */
+    /* layout: rings [PAIRS][896] u32 | queues [PAIRS][Q + 16] CodeT | tables */
     uint32_t *rings = reinterpret_cast<uint32_t *>(smem_raw);
-    double *sfq = reinterpret_cast<double *>(rings + GW_PAIRS * GW_RING);
-    CodeT *queues = reinterpret_cast<CodeT *>(sfq + P.fq_len);
+    CodeT *queues = reinterpret_cast<CodeT *>(rings + GW_PAIRS * GW_RING);
     const uint32_t Q = P.qlen;
     const uint8_t *tab = P.tab;
-    if (KIND == KIND_TREE) {
-        for (uint32_t i = tid; i < P.fq_len; i += blockDim.x) sfq[i] = P.fq[i];
-        if (TAB_SMEM) {
-            uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * (Q + 16));
-            stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
-            for (uint32_t i = tid; i < P.tab_len; i += blockDim.x) stab[i] = P.tab[i];
-            tab = stab;
-        }
+    if (KIND == KIND_TREE && TAB_SMEM) {
+        uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * (Q + 16));
+        stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
+        const uint32_t bytes = P.tab_len * (P.T > 1 ? 2u : 1u);
+        for (uint32_t i = tid; i < bytes; i += blockDim.x) stab[i] = P.tab[i];
+        tab = stab;
     }
     const int pair = warp % GW_PAIRS;
     const bool is_gen = warp < GW_PAIRS;
@@ -305,79 +362,28 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
         for (uint32_t r = lane; r < live; r += 32) {
             const uint64_t i = first + r0 + r;
             const uint32_t qb = kbase + r * d;
-#define MY_CODE(s_) ((uint32_t)queue[(qb + (s_)) & qmask])
-            uint32_t h = PCU_HASH_INIT;
-            uint32_t pay = 0;
+            uint32_t h = PCU_HASH_INIT, pay = 0;
             uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
             if (KIND == KIND_MOLD) {
-                for (uint32_t s = 0; s < d; ++s) {
-                    const uint32_t code = MY_CODE(s);
-                    h = hash_step(h, code, 0);
-                    if (tr) {
-                        const uint32_t rr = code / P.cols;
-                        tr[3 * s + 0] = (uint8_t)rr;
-                        tr[3 * s + 1] = (uint8_t)(code - rr * P.cols);
-                        tr[3 * s + 2] = 0;
-                    }
-                }
+                if (tr)
+                    h = walk_mold<true>(queue, qmask, qb, d, P.cols, tr);
+                else
+                    h = walk_mold<false>(queue, qmask, qb, d, P.cols, tr);
                 acc.d += 1;
             } else {
-                uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
+                const uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
                 int bias = P.bias ? P.bias[i] : P.bias_u;
+                const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
                 if (T == 1) {
-                    const uint32_t adv = 2 + P.gen_words;
-                    for (uint32_t s = 0; s < d; ++s) {
-                        const uint32_t code = MY_CODE(s);
-                        p += code; /* discard(row*cols + col): random-tree.hh:88-89 */
-                        bias += (int)((tab[p] >> 4) & 3u) - 1;
-                        p += adv;
-                        h = hash_step(h, code, 0);
-                        if (tr) {
-                            const uint32_t rr = code / P.cols;
-                            tr[3 * s + 0] = (uint8_t)rr;
-                            tr[3 * s + 1] = (uint8_t)(code - rr * P.cols);
-                            tr[3 * s + 2] = 0;
-                        }
-                    }
+                    if (tr)
+                        h = walk_tree1<true>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr);
+                    else
+                        h = walk_tree1<false>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr);
                 } else {
-                    uint32_t gb = p - P.gen_words; /* where the current chance strategies were drawn */
-                    for (uint32_t s = 0; s < d; ++s) {
-                        const uint32_t code = MY_CODE(s);
-                        const uint32_t st = code * T;
-                        const uint8_t *cell = tab + gb + 2 * st;
-                        int S = 0;
-                        for (uint32_t kk = 0; kk < T; ++kk) {
-                            int nk = (int)(cell[2 * kk] & 15u) + 1;
-                            if (nk * P.thr_q < P.thr_p * 10) nk = 0;
-                            S += nk;
-                        }
-                        const bool fallback = (S == 0);
-                        if (fallback) S = 1;
-                        double pp = P.pu;
-                        uint32_t ch = 0;
-                        for (uint32_t kk = 0; kk < T; ++kk) {
-                            int nk = (int)(cell[2 * kk] & 15u) + 1;
-                            if (nk * P.thr_q < P.thr_p * 10) nk = 0;
-                            if (fallback && kk == 0) nk = 1;
-                            pp -= sfq[(uint32_t)nk * P.fq_w + (uint32_t)S];
-                            if (pp <= 0) {
-                                ch = kk;
-                                break;
-                            }
-                        }
-                        p += st + ch;
-                        bias += (int)((tab[p] >> 4) & 3u) - 1;
-                        p += 2;
-                        gb = p;
-                        p += P.gen_words;
-                        h = hash_step(h, code, ch);
-                        if (tr) {
-                            const uint32_t rr = code / P.cols;
-                            tr[3 * s + 0] = (uint8_t)rr;
-                            tr[3 * s + 1] = (uint8_t)(code - rr * P.cols);
-                            tr[3 * s + 2] = (uint8_t)ch;
-                        }
-                    }
+                    if (tr)
+                        h = walk_treeT<true>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr);
+                    else
+                        h = walk_treeT<false>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr);
                 }
                 pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
                 acc.w += (pay == 2);
@@ -391,7 +397,6 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
             acc.h += h;
             acc.n += 1;
         }
-#undef MY_CODE
       }
       if (j + 2 < npass) {
           __syncwarp();
