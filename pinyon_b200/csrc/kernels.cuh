@@ -301,6 +301,8 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
     }
 }
 
+#include "lane.cuh"
+
 /* ------------------------------------------------------- integer-issue peak probe */
 
 /* VARIANT 0: LOP3 only; 1: LOP3 + SHF + IADD3 (all ALU pipe); 2: LOP3 + SHF + IMAD

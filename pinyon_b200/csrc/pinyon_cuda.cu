@@ -42,7 +42,7 @@ constexpr int PIN_BASE_WINDOW = 1024; /* word offset in pin_small of the staged 
 
 enum BufId {
     B_STATE_SEED, B_STATE_POS, B_TSEED, B_DEPTH, B_BIAS, B_MSEED, B_PAYOFF, B_TRAJ, B_HASH, B_SUMS,
-    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_COUNT
+    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_COUNT
 };
 
 }  // namespace
@@ -59,6 +59,7 @@ struct pcu_ctx {
     uint64_t launches = 0;
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
+    int force_warp = 0; /* test hook: keep distinct-root batches on k_warp instead of k_lane */
     int host_checkpoints = 0; /* test hook: brute-force checkpoints on the host instead of the jump kernels */
     DevBuf buf[B_COUNT];
     uint32_t *pin_small = nullptr; /* pinned staging: engine window out */
@@ -556,6 +557,60 @@ int launch_warp(pcu_ctx *ctx, const WarpParams &P) {
     return PCU_OK;
 }
 
+/* Draw-index bound and largest depth of a batch (k_lane's shared-memory column height).
+ * Batch-uniform positions and depths need no kernel. */
+int lane_bound(pcu_ctx *ctx, uint64_t n, const uint32_t *d_pos, uint32_t pos_u, const uint16_t *d_depth,
+               uint32_t depth_u, uint32_t gen_words, uint32_t per_step, uint64_t *words, uint64_t *dmax) {
+    if (!d_pos && !d_depth) {
+        *words = (uint64_t)pos_u - gen_words + (uint64_t)depth_u * per_step;
+        *dmax = depth_u;
+        return PCU_OK;
+    }
+    CU(ctx->buf[B_BOUND].ensure(16));
+    unsigned long long *o = reinterpret_cast<unsigned long long *>(ctx->buf[B_BOUND].p);
+    CU(cudaMemsetAsync(o, 0, 16, ctx->stream));
+    uint64_t blocks = std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx->sms * 8);
+    k_lane_bound<<<(unsigned)blocks, 256, 0, ctx->stream>>>(n, d_pos, pos_u, d_depth, depth_u, gen_words, per_step, o);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    unsigned long long h[2];
+    CU(cudaMemcpyAsync(h, o, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    CU(cudaStreamSynchronize(ctx->stream));
+    *words = h[0];
+    *dmax = h[1];
+    return PCU_OK;
+}
+
+/* k_lane: one warp per CTA, 32 rollouts per pass; shared memory = words x 32 lanes x 4 B. */
+template <int KIND, int MODE>
+int launch_lane(pcu_ctx *ctx, const WarpParams &W, uint32_t words, uint32_t dmax) {
+    LaneParams LP;
+    LP.w = W;
+    LP.words = words;
+    LP.dmax = dmax;
+    LP.mulc = 1812433253u;
+    LP.one = 1u;
+    CU(ctx->buf[B_L397].ensure(sizeof(uint32_t) * 2 * W.n));
+    LP.l397 = reinterpret_cast<uint32_t *>(ctx->buf[B_L397].p);
+    LP.lm397 = LP.l397 + W.n;
+    const size_t smem = std::max<size_t>((size_t)words * 32 * 4, 16);
+    int per_sm = (int)std::min<size_t>(32, (227 * 1024) / (smem + 1024));
+    if (per_sm < 1) per_sm = 1;
+    uint64_t blocks = std::min<uint64_t>((W.n + 31) / 32, (uint64_t)ctx->sms * per_sm);
+    if (blocks == 0) blocks = 1;
+    auto kern = k_lane<KIND, MODE>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    k_lane_pre<KIND, MODE><<<(unsigned)((W.n + 255) / 256), 256, 0, ctx->stream>>>(LP);
+    ctx->launches++;
+    kern<<<(unsigned)blocks, 32, smem, ctx->stream>>>(LP);
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
+
 int check_common(pcu_ctx *ctx, const void *batch, const pcu_model_rng *rng, const pcu_out *out) {
     if (!ctx) return PCU_ERR_INVALID;
     if (!batch || !rng || !out) return fail(ctx, PCU_ERR_INVALID, "null batch, rng or out");
@@ -661,6 +716,10 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "force_general")) {
         ctx->force_general = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "force_warp")) {
+        ctx->force_warp = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "host_checkpoints")) {
@@ -855,6 +914,17 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     W.traj_stride = out->traj_stride;
     W.traj_hash = od.hash;
     W.sums = od.sums;
+    /* lane-per-rollout kernel: transitions == 1 (draw positions depend on the action codes only) and every
+     * read inside the first refill of the state engine; mode P also needs 4 dmax model words below 227 */
+    uint64_t lane_words = 0, lane_dmax = 0;
+    bool lane = !ctx->force_warp && T == 1;
+    if (lane) {
+        const uint32_t per_step = gen_words + b->rows * b->cols - 1 + 2;
+        if ((rc = lane_bound(ctx, n, d_pos, b->state_pos_u, d_depth, b->depth_u, gen_words, per_step, &lane_words,
+                             &lane_dmax)))
+            return rc;
+        lane = lane_words <= MT_N - 1 && (rng->mode == PCU_MODEL_STREAM || 4 * lane_dmax <= MT_LAG - 3);
+    }
     if (rng->mode == PCU_MODEL_STREAM) {
         uint64_t total_steps = n * (uint64_t)b->depth_u;
         if (d_depth) {
@@ -864,12 +934,20 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16))) return rc;
         W.codes = ctx->buf[B_CODES].p;
         W.code_u16 = c16;
-        ctx->path = "warp_private_S";
-        if ((rc = launch_warp<KIND_TREE, 0>(ctx, W))) return rc;
+        ctx->path = lane ? "lane_private_S" : "warp_private_S";
+        if (lane)
+            rc = launch_lane<KIND_TREE, 0>(ctx, W, (uint32_t)lane_words, (uint32_t)lane_dmax);
+        else
+            rc = launch_warp<KIND_TREE, 0>(ctx, W);
+        if (rc) return rc;
     } else {
         W.model_seeds = d_mseed;
-        ctx->path = "warp_private_P";
-        if ((rc = launch_warp<KIND_TREE, 1>(ctx, W))) return rc;
+        ctx->path = lane ? "lane_private_P" : "warp_private_P";
+        if (lane)
+            rc = launch_lane<KIND_TREE, 1>(ctx, W, (uint32_t)lane_words, (uint32_t)lane_dmax);
+        else
+            rc = launch_warp<KIND_TREE, 1>(ctx, W);
+        if (rc) return rc;
     }
     return finish_all(ctx, out, n, od, rng);
 }
@@ -936,8 +1014,12 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         if ((rc = launch_warp<KIND_MOLD, 0>(ctx, W))) return rc;
     } else {
         W.model_seeds = d_mseed;
-        ctx->path = "warp_mold_P";
-        if ((rc = launch_warp<KIND_MOLD, 1>(ctx, W))) return rc;
+        uint64_t lw = 0, dmax = 0;
+        if ((rc = lane_bound(ctx, n, nullptr, 0, d_depth, b->depth_u, 0, 0, &lw, &dmax))) return rc;
+        const bool lane = !ctx->force_warp && 4 * dmax <= MT_LAG - 3;
+        ctx->path = lane ? "lane_mold_P" : "warp_mold_P";
+        rc = lane ? launch_lane<KIND_MOLD, 1>(ctx, W, 0, (uint32_t)dmax) : launch_warp<KIND_MOLD, 1>(ctx, W);
+        if (rc) return rc;
     }
     return finish_all(ctx, out, n, od, rng);
 }

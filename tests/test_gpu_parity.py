@@ -124,10 +124,57 @@ def test_tree_private_roots(ctx, oracle, mode, shape):
     got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=kw["depth"], state_seed=kw["state_seed"],
                    pre=kw["state_pre_discard"], tseed=kw["transition_seed"], bias=kw["payoff_bias"],
                    engine=None if mode == "P" else eng, model_seeds=mseeds)
-    assert ctx.last_path == "warp_private_" + mode
+    assert ctx.last_path == "warp_private_" + mode  # draw positions beyond the first refill, or T > 1
     check_same(got, exp, n)
     if mode == "S":
         assert engine_matches(eng, 21, 5 + 4 * int(kw["depth"].sum()), oracle)
+
+
+@pytest.mark.parametrize("mode", ["S", "P"])
+@pytest.mark.parametrize("shape", [(3, 3, 10, 150), (2, 5, 12, 60), (4, 4, 7, 250), (1, 1, 40, 0), (8, 9, 2, 20)])
+def test_tree_private_roots_lane(ctx, oracle, mode, shape):
+    """Distinct roots with one chance transition: the lane-per-rollout kernel,
+    ragged depths and positions, against the oracle and against the warp kernel."""
+    rows, cols, dmax, premax = shape
+    rng = np.random.default_rng(rows * 1000 + cols + dmax)
+    n = 777
+    kw = dict(state_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+              state_pre_discard=rng.integers(0, premax + 1, n).astype(np.uint32),
+              transition_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+              depth=rng.integers(1, dmax + 1, n).astype(np.uint32),
+              payoff_bias=rng.integers(-2, 3, n).astype(np.int32))
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64) if mode == "P" else None
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=1, model_seed=4,
+                                      model_pre_discard=9, model_seeds=mseeds, **kw)
+    for force_warp in (0, 1):
+        eng = Engine(4).discard(9)
+        ctx.set_option("force_warp", force_warp)
+        try:
+            got = run_tree(ctx, n, rows=rows, cols=cols, T=1, depth=kw["depth"], state_seed=kw["state_seed"],
+                           pre=kw["state_pre_discard"], tseed=kw["transition_seed"], bias=kw["payoff_bias"],
+                           engine=None if mode == "P" else eng, model_seeds=mseeds)
+        finally:
+            ctx.set_option("force_warp", 0)
+        assert ctx.last_path == ("warp_private_" if force_warp else "lane_private_") + mode
+        check_same(got, exp, n)
+        if mode == "S":
+            assert engine_matches(eng, 4, 9 + 4 * int(kw["depth"].sum()), oracle)
+
+
+@pytest.mark.parametrize("extra,path", [(0, "lane_private_S"), (1, "warp_private_S")])
+def test_tree_lane_boundary(ctx, oracle, extra, path):
+    """The lane kernel serves draw indices up to 622 (all of the first refill but its last word, whose
+    twist needs the refilled X[0]); one more pre-discarded draw sends the batch to the warp kernel."""
+    rows, cols, depth = 3, 3, 10
+    gen = 2 * rows * cols
+    pre = 623 - depth * (gen + rows * cols - 1 + 2) + extra  # bound = pre + depth * per_step
+    n = 300
+    seeds = np.arange(n, dtype=np.uint64) + np.uint64(2**32 - 100)  # seeds wrap mod 2^32 (random.hh:16)
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=1, depth=depth, model_seed=1,
+                                      state_seed=seeds, state_pre_discard=pre)
+    got = run_tree(ctx, n, rows=rows, cols=cols, depth=depth, state_seed=seeds, pre=pre, engine=Engine(1))
+    assert ctx.last_path == path
+    check_same(got, exp, n)
 
 
 def test_tree_general_path_equals_fused(ctx, oracle):
@@ -175,7 +222,7 @@ def test_mold_ragged(ctx, oracle, mode):
     sums = np.zeros(8, np.uint64)
     ctx.rollout_mold(n, n_actions=3, depth=depth.astype(np.uint16), engine=None if mode == "P" else eng,
                      model_seeds=mseeds, traj=traj, traj_stride=int(depth.max()), traj_hash=th, sums=sums)
-    assert ctx.last_path == "warp_mold_" + mode
+    assert ctx.last_path == ("lane_mold_P" if mode == "P" else "warp_mold_S")
     assert np.array_equal(traj, exp["traj"])
     assert np.array_equal(th, exp["traj_hash"])
     assert np.array_equal(sums, exp["sums"])
