@@ -36,6 +36,11 @@ WORKLOADS = {
                            kernel="k_stream2<TREE,u8,tab_smem>"),
     "tree_d20_9x9x3": dict(kind="tree", rows=9, cols=9, T=3, depth=20, log2n=24, ops_step=4920.0, ops_exec=80.0,
                            kernel="k_stream2<TREE,u8,tab_smem>"),
+    # distinct roots (state_seed_i = i): every rollout owns a private state engine, so the
+    # kernel pays the 623-step seeding chain per rollout.  ops_setup = 2492, ops_exec per ROLLOUT here:
+    # chain 397*3 + lock-step 227*(3+3+5) + tail 56*(3+5) + play 10*45.
+    "tree_d10_3x3x1_dr": dict(kind="tree", rows=3, cols=3, T=1, depth=10, log2n=24, ops_step=318.0, ops_setup=2492.0,
+                              ops_exec=458.6, dr=True, kernel="k_lane_pre + k_lane<TREE,S>"),
     "mold_2_10": dict(kind="mold", rows=2, cols=2, T=1, depth=10, log2n=24, ops_step=104.0, ops_exec=70.0,
                       kernel="k_stream2<MOLD,u8>"),
 }
@@ -46,8 +51,10 @@ WORDS_PER_STEP = 4  # two random_int per step, two 32-bit draws each (random.hh:
 def describe(w, n):
     if w["kind"] == "mold":
         return f"MoldState n_actions={w['rows']} max_depth={w['depth']}, batch {n} per GPU, mode S (one model prng{{0}})"
+    root = ("DISTINCT roots state_seed_i = i, transition_seed_i = i*0x9E3779B97F4A7C15 (SURVEY M1-DR)" if w.get("dr")
+            else "root prng{0}")
     return (f"RandomTree depth_bound={w['depth']} {w['rows']}x{w['cols']} actions {w['T']} chance transition(s), "
-            f"root prng{{0}}, batch {n} (2^{w['log2n']}) per GPU, mode S (one model prng{{0}} consumed in index order)")
+            f"{root}, batch {n} (2^{w['log2n']}) per GPU, mode S (one model prng{{0}} consumed in index order)")
 
 
 class ClockSampler:
@@ -210,11 +217,22 @@ def run_ours(args, w):
     stream = torch.cuda.current_stream()
     ctx.set_stream(stream.cuda_stream)
 
+    dr_dev, dr_host = {}, {}
+    if w.get("dr"):
+        first = shard.first
+        idx = np.arange(first, first + n, dtype=np.uint64)
+        ts = idx * np.uint64(0x9E3779B97F4A7C15)
+        dr_host = dict(state_seed=ctx.pinned(n, np.uint64), transition_seed=ctx.pinned(n, np.uint64))
+        dr_host["state_seed"][:] = idx
+        dr_host["transition_seed"][:] = ts
+        dr_dev = {k: torch.from_numpy(v.view(np.int64)).to(dev) for k, v in dr_host.items()}
+
     def call(payoff, sums):
         eng = base_engine.copy()
         if w["kind"] == "tree":
+            extra = dr_dev if isinstance(payoff, torch.Tensor) else dr_host
             ctx.rollout_random_tree(n, rows=w["rows"], cols=w["cols"], transitions=w["T"], depth=depth, engine=eng,
-                                    payoff=payoff, sums=sums)
+                                    payoff=payoff, sums=sums, **extra)
         else:
             ctx.rollout_mold(n, n_actions=w["rows"], depth=depth, engine=eng, payoff=payoff, sums=sums)
 
@@ -281,11 +299,31 @@ def run_ours(args, w):
         int_peak = max(ctx.int_peak(5, 5), ctx.int_peak(2, 5), int_peak_alu)
         ms_step = dev_ms / args.steps
         k_ms = float(np.mean(kernel_ms))
-        ops_launch = w["ops_step"] * depth * n          # SURVEY.md §8(d) algorithmic figure
-        exe_launch = w["ops_exec"] * depth * n          # what the shared-stream kernel really has to do
+        ops_launch = (w["ops_step"] * depth + w.get("ops_setup", 0.0)) * n   # SURVEY.md §8(d) algorithmic figure
+        exe_launch = w["ops_exec"] * depth * n          # what the kernel really has to do
         achieved = ops_launch / (k_ms * 1e-3)
         executed = exe_launch / (k_ms * 1e-3)
         hbm_bytes = float(n)  # one payoff byte per rollout; inputs are batch-uniform scalars
+        h2d = 624 * 4 + 8
+        if w.get("dr"):
+            hbm_bytes = float(n) * (1 + 8 + depth + 8)  # payoff + state seed + action codes + x[397] write/read
+            h2d += 8 * n  # state seeds (transition seeds are not staged when transitions == 1)
+        note = ("achieved = algorithmic int32 ops (SURVEY.md 8(d): %.0f per rollout-step, counted for a PRIVATE state "
+                "stream) / the rollout kernel's own CUDA-event time; peak = int-issue microbenchmark measured in this "
+                "run (LOP3 only %.1f, LOP3:IMAD 1:1 %.1f Gop/s). " % (w["ops_step"], int_peak_alu / 1e9, int_peak / 1e9))
+        if w.get("dr"):
+            note += ("DISTINCT-ROOT run: every rollout seeds and advances its own state engine (+%.0f ops per rollout "
+                     "for the seeding chain, included in achieved); `executed` counts the %.0f ops per rollout the "
+                     "lane kernels really issue (only the first-refill words a rollout can reach are twisted). "
+                     "kernel_ms brackets k_lane_pre + k_lane; the model-stream code generator (k_gen_codes2 + "
+                     "jump-ahead) runs before it and is in ms_per_step only"
+                     % (w["ops_setup"], w["ops_exec"] * depth))
+        else:
+            note += ("SHARED-STREAM run: every rollout of the batch shares the root's state seed, so the kernel serves "
+                     "the state stream from a shared-memory table and only has to generate the model stream: "
+                     "`executed` counts those %.0f ops per step (4 words x (4 twist + 8 temper) + 2 u64 mod n x 9 + "
+                     "table walk) and is the figure that measures the kernel; frac > executed.frac is the shortcut's "
+                     "gain, not kernel quality" % w["ops_exec"])
         line = {
             "metric": "rollouts/sec", "value": value, "unit": "rollouts/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
@@ -294,7 +332,7 @@ def run_ours(args, w):
                        "parallelism": f"dp{world}: rollout-index shards of one model stream, NCCL all-reduce of sums only",
                        "streams_per_sm": args.streams_per_sm or 4},
             "rollout_steps_per_sec": value * depth,
-            "e2e": {"value": e2e, "unit": "rollouts/s", "h2d_bytes_per_step": 624 * 4 + 8,
+            "e2e": {"value": e2e, "unit": "rollouts/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": n + 64 + 624 * 4, "rollout_steps_per_sec": e2e * depth},
             "gpu_launches": int(launches),
             "clocks": clocks,
@@ -304,15 +342,7 @@ def run_ours(args, w):
                          "frac": achieved / int_peak, "traffic": None,
                          "executed": {"ops_per_step": w["ops_exec"], "achieved": executed / 1e9,
                                       "frac": executed / int_peak, "frac_of_alu_pipe": executed / int_peak_alu},
-                         "note": ("achieved = algorithmic int32 ops (SURVEY.md §8(d): %.0f per rollout-step, counted for a "
-                                  "PRIVATE state stream) / the rollout kernel's own CUDA-event time; peak = int-issue "
-                                  "microbenchmark measured in this run (LOP3 only %.1f, LOP3:IMAD 1:1 %.1f Gop/s). "
-                                  "SHARED-STREAM run: every rollout of the batch shares the root's state seed, so the "
-                                  "kernel serves the state stream from a shared-memory table and only has to generate "
-                                  "the model stream: `executed` counts those %.0f ops per step (4 words x (4 twist + "
-                                  "8 temper) + 2 u64 mod n x 9 + table walk) and is the figure that measures the "
-                                  "kernel; frac > executed.frac is the shortcut's gain, not kernel quality"
-                                  % (w["ops_step"], int_peak_alu / 1e9, int_peak / 1e9, w["ops_exec"])),
+                         "note": note,
                          "hbm": {"achieved": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
                                  "unit": "GB/s", "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
                                  "peak_source": peak_kind}},

@@ -92,19 +92,35 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
 
     unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_s = 0;
     const uint64_t chunks = (P.n + 31) / 32;
+    /* seeds of the NEXT chunk are fetched one chunk ahead: a warp is alone on its scheduler most of the time */
+    uint32_t e_nx = 0, l_nx = 0, em_nx = 0, lm_nx = 0;
+    auto fetch = [&](uint64_t chunk) {
+        if (chunk >= chunks) return;
+        const uint64_t j = chunk * 32 + lane < P.n ? chunk * 32 + lane : P.n - 1;
+        if (KIND == KIND_TREE) {
+            e_nx = (uint32_t)(P.state_seed ? P.state_seed[j] : P.state_seed_u);
+            l_nx = LP.l397[j]; /* phase 1 ran in k_lane_pre */
+        }
+        if (MODE == 1) {
+            em_nx = (uint32_t)P.model_seeds[j];
+            lm_nx = LP.lm397[j];
+        }
+    };
+    fetch(blockIdx.x);
     for (uint64_t chunk = blockIdx.x; chunk < chunks; chunk += gridDim.x) {
         const uint64_t i = chunk * 32 + lane;
         const bool live = i < P.n;
         const uint64_t ii = live ? i : P.n - 1; /* idle lanes replay the last rollout, write nothing */
-        uint32_t e = 0, l = 0, em = 0, lm = 0;
+        uint32_t e = e_nx, l = l_nx, em = em_nx, lm = lm_nx;
+        fetch(chunk + gridDim.x);
+        const uint32_t d = P.depth ? P.depth[ii] : P.depth_u;
+        uint32_t pos = 0;
+        int bias = 0;
         if (KIND == KIND_TREE) {
-            e = (uint32_t)(P.state_seed ? P.state_seed[ii] : P.state_seed_u);
-            l = LP.l397[ii]; /* phase 1 ran in k_lane_pre */
+            pos = (P.state_pos ? P.state_pos[ii] : P.state_pos_u) - P.gen_words;
+            bias = P.bias ? P.bias[ii] : P.bias_u;
         }
-        if (MODE == 1) {
-            em = (uint32_t)P.model_seeds[ii];
-            lm = LP.lm397[ii];
-        }
+        const uint64_t soff = (MODE == 0) ? (P.step_off ? P.step_off[ii] : ii * (uint64_t)P.depth_u) : 0;
         if (KIND == KIND_TREE) {
             __syncwarp();
             /* ---- phase 2: X[k], k < 227, from the two chains in lock-step */
@@ -132,14 +148,7 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
         }
 
         /* ---- phase 4: play */
-        const uint32_t d = P.depth ? P.depth[ii] : P.depth_u;
-        uint32_t pos = 0;
-        int bias = 0;
-        if (KIND == KIND_TREE) {
-            pos = (P.state_pos ? P.state_pos[ii] : P.state_pos_u) - P.gen_words;
-            bias = P.bias ? P.bias[ii] : P.bias_u;
-        }
-        const uint64_t soff = (MODE == 0) ? (P.step_off ? P.step_off[ii] : ii * (uint64_t)P.depth_u) : 0;
+        __syncwarp();
         uint32_t h = PCU_HASH_INIT;
         uint8_t *tr = (P.traj && live) ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
         uint32_t dloop = d;

@@ -814,7 +814,8 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     if ((rc = stage_in(ctx, b->mem, b->state_pos, n, B_STATE_POS, &d_pos))) return rc;
     if ((rc = stage_in(ctx, b->mem, b->payoff_bias, n, B_BIAS, &d_bias))) return rc;
     if ((rc = stage_in(ctx, b->mem, b->state_seed, n, B_STATE_SEED, &d_sseed))) return rc;
-    if ((rc = stage_in(ctx, b->mem, b->transition_seed, n, B_TSEED, &d_tseed))) return rc;
+    /* prng{transition_seed} only decides between chance actions (random-tree.hh:118-133): unused when T == 1 */
+    if ((rc = stage_in(ctx, b->mem, T > 1 ? b->transition_seed : nullptr, n, B_TSEED, &d_tseed))) return rc;
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
