@@ -101,6 +101,10 @@ struct WarpParams {
     uint32_t traj_stride;
     uint32_t *traj_hash;
     unsigned long long *sums;
+    /* slab of rollouts [i0, i1) seeded by k_seed_pre (seed.cuh): arrays indexed by i - i0 */
+    uint64_t i0, i1;
+    const uint32_t *xs_slab, *xm_slab;
+    const double *pu_slab;
 };
 
 /* A private MT19937 held in shared memory by one warp.  x[] is libstdc++'s state
@@ -110,18 +114,46 @@ struct WarpMT {
     long long base;
 };
 
+/* One refill of the warp's engine (bits/random.tcc _M_gen_rand), in place: x[w] <- x[w+397 mod 624]
+ * ^ twist(x[w], x[w+1 mod 624]) for w = 0..623 in order.  Five groups of <= 128 words; a group reads
+ * every operand before it writes anything (its writes would clobber the `b` operand of the word
+ * before them), and since a group is shorter than 227 words the x[w-227] operands of later groups are
+ * already NEW.  All addresses are lane + constant after unrolling; the only per-lane selects are the
+ * sub-block where w+397 crosses 624 (w = 224..255) and the half sub-block at the end. */
 __device__ __forceinline__ void wmt_twist(WarpMT &e, int lane) {
-#pragma unroll 1
-    for (int sub = 0; sub < 20; ++sub) {
-        const int k = sub * 32 + lane;
-        uint32_t a = 0, b = 0, c = 0;
-        if (k < MT_N) {
-            a = e.x[k];
-            b = e.x[k + 1 == MT_N ? 0 : k + 1];
-            c = e.x[k + MT_M >= MT_N ? k - MT_LAG : k + MT_M];
+    uint32_t *xl = e.x + lane;
+#pragma unroll
+    for (int g = 0; g < 5; ++g) {
+        uint32_t a[4], b[4], c[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const int w0 = g * 128 + m * 32;
+            if (w0 >= MT_N) continue;
+            if (w0 + 32 <= MT_N) {
+                a[m] = xl[w0];
+                b[m] = xl[w0 + 1];
+                if (w0 + 31 < MT_LAG)
+                    c[m] = xl[w0 + MT_M];
+                else if (w0 >= MT_LAG)
+                    c[m] = xl[w0 - MT_LAG];
+                else
+                    c[m] = xl[(w0 + lane < MT_LAG) ? w0 + MT_M : w0 - MT_LAG];
+            } else { /* w0 = 608: words 608..623 on lanes 0..15; b of word 623 is the new x[0] */
+                a[m] = b[m] = c[m] = 0;
+                if (lane < MT_N - w0) {
+                    a[m] = xl[w0];
+                    b[m] = (w0 + lane + 1 == MT_N) ? e.x[0] : xl[w0 + 1];
+                    c[m] = xl[w0 - MT_LAG];
+                }
+            }
         }
         __syncwarp();
-        if (k < MT_N) e.x[k] = mt_twist(a, b, c);
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const int w0 = g * 128 + m * 32;
+            if (w0 >= MT_N) continue;
+            if (w0 + 32 <= MT_N || lane < MT_N - w0) xl[w0] = mt_twist_dev(a[m], b[m], c[m]);
+        }
         __syncwarp();
     }
     e.base += MT_N;
@@ -161,40 +193,22 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
     const uint64_t warp0 = (uint64_t)blockIdx.x * warps_per_block + wib;
     const uint64_t stride = (uint64_t)gridDim.x * warps_per_block;
 
-    for (uint64_t i = warp0; i < P.n; i += stride) {
+    for (uint64_t i = P.i0 + warp0; i < P.i1; i += stride) {
         const uint32_t d = P.depth ? P.depth[i] : P.depth_u;
-        /* ---- seed: lane 0 the state engine, lane 1 the model engine, lane 2 the
-         * throw-away prng{transition_seed} of random-tree.hh:118 (only its first two
-         * draws are ever used, and they are the same every step). */
-        uint32_t v = 0;
+        /* ---- the seeded engines of this rollout, 20 coalesced 128-byte reads each */
+        __syncwarp();
         if (KIND == KIND_TREE) {
-            const uint64_t ss = P.state_seed ? P.state_seed[i] : P.state_seed_u;
-            const uint64_t ts = P.tseed ? P.tseed[i] : P.tseed_u;
-            v = (lane == 2) ? (uint32_t)ts : (uint32_t)ss;
+            const uint32_t *src = P.xs_slab + (i - P.i0) * MT_N;
+#pragma unroll 5
+            for (int k = lane; k < MT_N; k += 32) xs[k] = src[k];
         }
-        if (MODE == 1 && lane == 1) v = (uint32_t)P.model_seeds[i];
-        uint32_t *dst = nullptr;
-        if (KIND == KIND_TREE && lane == 0) dst = xs;
-        if (MODE == 1 && lane == 1) dst = xm;
-        const uint32_t t0 = v;
-        uint32_t t1 = 0, t2 = 0, t397 = 0, t398 = 0;
-        if (dst) dst[0] = v;
-#pragma unroll 4
-        for (uint32_t k = 1; k < MT_N; ++k) {
-            v = mt_init_step(v, k);
-            if (dst) dst[k] = v;
-            if (k == 1) t1 = v;
-            if (k == 2) t2 = v;
-            if (k == 397) t397 = v;
-            if (k == 398) t398 = v;
+        if (MODE == 1) {
+            const uint32_t *src = P.xm_slab + (i - P.i0) * MT_N;
+#pragma unroll 5
+            for (int k = lane; k < MT_N; k += 32) xm[k] = src[k];
         }
         double pu = 0.0;
-        if (KIND == KIND_TREE && P.T > 1) {
-            const uint32_t o0 = mt_temper(mt_twist(t0, t1, t397));
-            const uint32_t o1 = mt_temper(mt_twist(t1, t2, t398));
-            pu = prng_uniform_from_words(o0, o1);
-            pu = __shfl_sync(PCU_FULL, pu, 2);
-        }
+        if (KIND == KIND_TREE && P.T > 1) pu = P.pu_slab[i - P.i0];
         __syncwarp();
         WarpMT es = {xs, -(long long)MT_N};
         WarpMT em = {xm, -(long long)MT_N};
@@ -302,6 +316,7 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
 }
 
 #include "lane.cuh"
+#include "seed.cuh"
 
 /* ------------------------------------------------------- integer-issue peak probe */
 

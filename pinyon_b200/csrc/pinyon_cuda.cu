@@ -42,7 +42,7 @@ constexpr int PIN_BASE_WINDOW = 1024; /* word offset in pin_small of the staged 
 
 enum BufId {
     B_STATE_SEED, B_STATE_POS, B_TSEED, B_DEPTH, B_BIAS, B_MSEED, B_PAYOFF, B_TRAJ, B_HASH, B_SUMS,
-    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_COUNT
+    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_SEEDED, B_COUNT
 };
 
 }  // namespace
@@ -537,22 +537,65 @@ int scan_depths(pcu_ctx *ctx, const uint16_t *d_depth, uint64_t n, const uint64_
     return PCU_OK;
 }
 
+/* k_warp over slabs of rollouts: k_seed_pre seeds a slab's private engines lane-per-rollout into an HBM
+ * scratch (2496 B per engine), k_warp plays the slab one rollout per warp. */
+constexpr uint64_t WARP_SLAB = 1ull << 17;
+
 template <int KIND, int MODE>
-int launch_warp(pcu_ctx *ctx, const WarpParams &P) {
+int launch_warp(pcu_ctx *ctx, const WarpParams &P0) {
     constexpr int ENGINES = (KIND == KIND_TREE ? 1 : 0) + (MODE == 1 ? 1 : 0);
     const int warps = 8;
     const size_t smem = (size_t)warps * MT_N * 4 * (ENGINES ? ENGINES : 1);
-    uint64_t blocks = (P.n + warps - 1) / warps;
-    const uint64_t cap = (uint64_t)ctx->sms * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks == 0) blocks = 1;
     auto kern = k_warp<KIND, MODE>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const uint64_t slab = ENGINES ? std::min<uint64_t>(P0.n, WARP_SLAB) : P0.n;
+    const bool want_pu = KIND == KIND_TREE && P0.T > 1;
+    uint32_t *xs = nullptr, *xm = nullptr;
+    double *pu = nullptr;
+    if (ENGINES) {
+        const size_t eng = sizeof(uint32_t) * MT_N * slab;
+        CU(ctx->buf[B_SEEDED].ensure(eng * ENGINES + sizeof(double) * slab));
+        char *base = reinterpret_cast<char *>(ctx->buf[B_SEEDED].p);
+        pu = reinterpret_cast<double *>(base);
+        xs = reinterpret_cast<uint32_t *>(base + sizeof(double) * slab);
+        xm = (KIND == KIND_TREE) ? xs + MT_N * slab : xs;
+    }
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    kern<<<(unsigned)blocks, warps * 32, smem, ctx->stream>>>(P);
+    for (uint64_t i0 = 0; i0 < P0.n; i0 += slab) {
+        WarpParams P = P0;
+        P.i0 = i0;
+        P.i1 = std::min<uint64_t>(P0.n, i0 + slab);
+        const uint64_t cnt = P.i1 - P.i0;
+        if (ENGINES) {
+            SeedParams S;
+            memset(&S, 0, sizeof(S));
+            S.i0 = i0;
+            S.count = cnt;
+            S.state_seed = P0.state_seed;
+            S.state_seed_u = P0.state_seed_u;
+            S.model_seeds = MODE == 1 ? P0.model_seeds : nullptr;
+            S.tseed = P0.tseed;
+            S.tseed_u = P0.tseed_u;
+            S.want_state = KIND == KIND_TREE;
+            S.want_model = MODE == 1;
+            S.want_pu = want_pu;
+            S.mulc = 1812433253u;
+            S.xs = xs;
+            S.xm = xm;
+            S.pu = pu;
+            k_seed_pre<<<(unsigned)((cnt + 127) / 128), 128, 0, ctx->stream>>>(S);
+            ctx->launches++;
+            P.xs_slab = xs;
+            P.xm_slab = xm;
+            P.pu_slab = pu;
+        }
+        uint64_t blocks = std::min<uint64_t>((cnt + warps - 1) / warps, (uint64_t)ctx->sms * 8);
+        if (blocks == 0) blocks = 1;
+        kern<<<(unsigned)blocks, warps * 32, smem, ctx->stream>>>(P);
+        ctx->launches++;
+    }
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->ev_valid = true;
-    ctx->launches++;
     CU(cudaGetLastError());
     return PCU_OK;
 }
