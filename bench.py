@@ -182,6 +182,103 @@ def run_reference_arm(args, w):
     print(json.dumps(line), flush=True)
 
 
+# ------------------------------------------------------------------ search workload (M4)
+
+SEARCH_BIN = ROOT / "tests" / "cpp" / "_bin" / "bench_search"
+
+
+def run_search_binary(impl, gpu_id, seed, leaves, iters, warmup):
+    """tests/cpp/bench_search.cc: the reference's unmodified OffPolicy<Exp3<...>> over the reference model
+    (impl 'ref') or the drop-in GPU model (impl 'gpu'); prebuilt next to the reference headers."""
+    if not SEARCH_BIN.exists():
+        raise RuntimeError(f"{SEARCH_BIN} missing: build it with `python tests/cpp/build.py` next to the reference")
+    res = subprocess.run([str(SEARCH_BIN), impl, str(gpu_id), str(seed), str(leaves), str(iters), str(warmup)],
+                         capture_output=True, text=True, timeout=1200)
+    if res.returncode != 0:
+        raise RuntimeError(f"bench_search {impl} failed: {res.stderr[-2000:]}")
+    return json.loads(res.stdout.strip().splitlines()[-1])
+
+
+def run_search(args):
+    """BASELINE.json configs[4] / SURVEY 8(d) M4: OffPolicy<Exp3<MonteCarloModel<RandomTree>>> on M1's root, 4096
+    leaves per batched inference, ROOT-PARALLEL over the GPUs: rank r searches its own tree with device prng{r},
+    root statistics (exp3.hh:9-16) are summed over ranks (the path's only collective).  A step = one learner
+    iteration (4096 tree descents on the host + one batched leaf evaluation on the GPU + the tree update)."""
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    reference = args.impl == "reference"
+    if reference and rank != 0:
+        return
+    if world > 1 and not reference:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    leaves = 4096
+    if not reference:
+        torch.cuda.set_device(local)
+        # parity first: equal seeds and iteration counts must give the same tree (ref on the host cores, gpu here)
+        if rank == 0:
+            a = run_search_binary("ref", 0, 0, leaves, 3, 0)
+            b = run_search_binary("gpu", local, 0, leaves, 3, 0)
+            keys = ("nodes", "visits", "value_total_row", "row_visits", "col_visits")
+            assert all(a[k] == b[k] for k in keys), ("GPU search diverged from the reference", a, b)
+        if world > 1:
+            dist.barrier()
+    sampler = ClockSampler(local)
+    if not reference:
+        sampler.start()
+    t0 = time.time()
+    out = run_search_binary("ref" if reference else "gpu", local, rank, leaves, args.steps, args.warmup)
+    t1 = time.time()
+    sec = out["seconds"]
+    stats = [out["nodes"], out["visits"], int(round(2 * out["value_total_row"])), *out["row_visits"], *out["col_visits"]]
+    if not reference:
+        clocks = sampler.stop(t0, t1)
+        t = torch.tensor([sec], dtype=torch.float64, device="cuda")
+        tot = torch.tensor(stats, dtype=torch.int64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        sec = float(t.item())
+        stats = tot.cpu().tolist()
+    if rank == 0:
+        n = world if not reference else 1
+        value = leaves * args.steps * n / sec
+        line = {
+            "metric": "search leaves/sec", "value": value, "unit": "leaves/s", "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1e3 * sec / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+            "config": {"workload": "OffPolicy<Exp3<MonteCarloModel<RandomTree>>> (off-policy.hh:83-109) on root "
+                                   "RandomTree{prng{0},10,3,3,1}, 4096 leaves per batched inference, gamma 0.01, "
+                                   "model prng{0}, device prng{rank}; one search tree per GPU (root-parallel), root "
+                                   "statistics summed over ranks",
+                       "parallelism": f"root-parallel x{n}", "l2": "inputs differ every step (the tree grows)"},
+            "root_stats_sum": {"nodes": stats[0], "visits": stats[1], "value_total_row_x2": stats[2],
+                               "row_visits": stats[3:6], "col_visits": stats[6:9]},
+        }
+        if reference:
+            line["impl"] = "reference"
+            line["cpu_baseline"] = {"value": value, "unit": "leaves/s", "cores": 1, "kind": "reference",
+                                    "sample": f"{args.steps} learner iterations of 4096 leaves, the reference's own "
+                                              "single-threaded OffPolicy + MonteCarloModel"}
+            line["e2e"] = {"value": value, "unit": "leaves/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+        else:
+            # the whole search IS the end-to-end path: host tree walk, H2D of the SoA leaf batch, rollouts, D2H of payoffs
+            line["e2e"] = {"value": value, "unit": "leaves/s", "h2d_bytes_per_step": leaves * 26 + 624 * 4 + 8,
+                           "d2h_bytes_per_step": leaves + 64 + 624 * 4}
+            line["gpu_launches"] = None
+            line["clocks"] = clocks
+            line["note"] = ("host-bound: 4096 tree descents and state copies per step run on ONE host thread in the "
+                            "reference's OffPolicy; the GPU evaluates the 4096 leaves in one call. parity: ref == gpu "
+                            "root statistics checked for 3 learner iterations before timing")
+        print(json.dumps(line), flush=True)
+    if world > 1 and not reference:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
 # ------------------------------------------------------------------------------ our arm
 
 
@@ -366,12 +463,14 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["search_offpolicy"])
     ap.add_argument("--log2n", type=int, default=0, help="override rollouts per GPU (log2)")
     ap.add_argument("--streams-per-sm", type=int, default=0, help="model-stream generator warps per SM (default 4)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.workload == "search_offpolicy":
+        return run_search(args)
     w = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference_arm(args, w)

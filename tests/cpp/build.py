@@ -13,34 +13,45 @@ HERE = Path(__file__).resolve().parent
 ROOT = HERE.parent.parent
 REFERENCE = Path(os.environ.get("PINYON_REFERENCE", "/root/reference"))
 BIN = HERE / "_bin" / "test_dropin"
-SOURCES = [HERE / "test_dropin.cc", *sorted((ROOT / "include" / "pinyon_cuda").glob("*.hh")), ROOT / "include" / "pinyon_cuda.h"]
+BENCH_BIN = HERE / "_bin" / "bench_search"  # bench.py --workload search_offpolicy (BASELINE configs[4])
+HEADERS = [*sorted((ROOT / "include" / "pinyon_cuda").glob("*.hh")), ROOT / "include" / "pinyon_cuda.h"]
+SOURCES = [HERE / "test_dropin.cc", *HEADERS]
 
 
 def reference_available() -> bool:
     return (REFERENCE / "src" / "model" / "monte-carlo-model.hh").exists()
 
 
-def is_stale() -> bool:
-    if not BIN.exists():
+def is_stale(binary: Path = BIN, source: Path = HERE / "test_dropin.cc") -> bool:
+    if not binary.exists():
         return True
-    t = BIN.stat().st_mtime
-    return any(p.stat().st_mtime > t for p in SOURCES)
+    t = binary.stat().st_mtime
+    return any(p.stat().st_mtime > t for p in [source, *HEADERS])
 
 
-def build(force: bool = False) -> Path:
+def _compile(binary: Path, source: Path, force: bool) -> Path:
     if not reference_available():
-        raise RuntimeError(f"{REFERENCE} is not present: test_dropin can only be built next to the reference")
-    if not force and not is_stale():
-        return BIN
-    BIN.parent.mkdir(exist_ok=True)
+        raise RuntimeError(f"{REFERENCE} is not present: {binary.name} can only be built next to the reference")
+    if not force and not is_stale(binary, source):
+        return binary
+    binary.parent.mkdir(exist_ok=True)
     cmd = ["g++", "-std=c++23", "-O2", "-pthread", "-I", str(ROOT / "oracle" / "shim"), "-I", str(REFERENCE / "src"),
-           "-I", str(ROOT / "include"), "-o", str(BIN), str(HERE / "test_dropin.cc"), "-L", str(ROOT / "pinyon_b200"),
+           "-I", str(ROOT / "include"), "-o", str(binary), str(source), "-L", str(ROOT / "pinyon_b200"),
            "-lpinyon_cuda", "-Wl,-rpath,$ORIGIN/../../../pinyon_b200"]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("g++ failed:\n" + res.stderr[-4000:])
-    return BIN
+    return binary
+
+
+def build(force: bool = False) -> Path:
+    return _compile(BIN, HERE / "test_dropin.cc", force)
+
+
+def build_bench(force: bool = False) -> Path:
+    return _compile(BENCH_BIN, HERE / "bench_search.cc", force)
 
 
 if __name__ == "__main__":
     print(build(force=True))
+    print(build_bench(force=True))

@@ -46,3 +46,26 @@ def test_dropin_matches_reference_on_gpu():
     out = _run("--gpu")
     for part in ("single inference ok", "batch inference ok", "TreeBandit<Exp3>", "OffPolicy<Exp3>", "threaded copies ok"):
         assert part in out
+
+
+@pytest.mark.gpu
+def test_search_bench_binary_ref_equals_gpu():
+    """tests/cpp/bench_search.cc (bench.py --workload search_offpolicy, BASELINE configs[4]): the reference's
+    OffPolicy<Exp3> with 4096-leaf batches builds the same tree over the GPU model as over the reference model."""
+    import json
+
+    _binary()
+    if cpp_build.reference_available():
+        binary = cpp_build.build_bench()
+    elif cpp_build.BENCH_BIN.exists():
+        binary = cpp_build.BENCH_BIN
+    else:
+        pytest.skip("bench_search was not prebuilt and the reference headers are absent")
+    outs = []
+    for impl in ("ref", "gpu"):
+        res = subprocess.run([str(binary), impl, "0", "5", "4096", "2", "1"], capture_output=True, text=True, timeout=600)
+        assert res.returncode == 0, res.stderr[-2000:]
+        outs.append(json.loads(res.stdout.strip().splitlines()[-1]))
+    for key in ("nodes", "visits", "value_total_row", "row_visits", "col_visits"):
+        assert outs[0][key] == outs[1][key], key
+    assert outs[0]["nodes"] == 3 * 4096
