@@ -298,6 +298,8 @@ def run_ours(args, w):
     ctx = Context(local)
     if args.streams_per_sm:
         ctx.set_option("streams_per_sm", args.streams_per_sm)
+    if args.no_zero_copy:
+        ctx.set_option("zero_copy", 0)
     n = 1 << (args.log2n or w["log2n"])
     depth = w["depth"]
 
@@ -466,6 +468,7 @@ def main():
     ap.add_argument("--workload", default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS) + ["search_offpolicy"])
     ap.add_argument("--log2n", type=int, default=0, help="override rollouts per GPU (log2)")
     ap.add_argument("--streams-per-sm", type=int, default=0, help="model-stream generator warps per SM (default 4)")
+    ap.add_argument("--no-zero-copy", action="store_true", help="e2e: stage payoffs in HBM and copy them back")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

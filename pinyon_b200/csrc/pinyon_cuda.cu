@@ -59,6 +59,7 @@ struct pcu_ctx {
     uint64_t launches = 0;
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
+    int zero_copy = 1; /* payoffs of large batches go straight to pinned host buffers */
     int force_warp = 0; /* test hook: keep distinct-root batches on k_warp instead of k_lane */
     int host_checkpoints = 0; /* test hook: brute-force checkpoints on the host instead of the jump kernels */
     DevBuf buf[B_COUNT];
@@ -290,6 +291,7 @@ int copy_back(pcu_ctx *ctx, int mem, T *dst, const T *dev, uint64_t count) {
 }
 
 struct OutDev {
+    bool payoff_direct = false; /* payoff points at the caller's pinned host buffer (zero-copy stores) */
     uint8_t *payoff = nullptr;
     uint8_t *traj = nullptr;
     uint32_t *hash = nullptr;
@@ -298,7 +300,19 @@ struct OutDev {
 
 int prepare_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, OutDev &od) {
     int rc;
-    if ((rc = stage_out(ctx, out->mem, out->payoff_x2, n, B_PAYOFF, &od.payoff))) return rc;
+    /* Large batches into PINNED host memory: the kernels store the payoff bytes straight into the caller's
+     * buffer over PCIe while they run, instead of a device buffer + a D2H copy after the last rollout. */
+    od.payoff_direct = false;
+    if (ctx->zero_copy && out->mem == PCU_MEM_HOST && out->payoff_x2 && n >= (1ull << 20)) {
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, out->payoff_x2) == cudaSuccess && at.type == cudaMemoryTypeHost &&
+            at.devicePointer) {
+            od.payoff = static_cast<uint8_t *>(at.devicePointer);
+            od.payoff_direct = true;
+        }
+        cudaGetLastError(); /* pageable memory reports an error on some drivers: not ours */
+    }
+    if (!od.payoff_direct && (rc = stage_out(ctx, out->mem, out->payoff_x2, n, B_PAYOFF, &od.payoff))) return rc;
     if ((rc = stage_out(ctx, out->mem, out->traj, n * (uint64_t)out->traj_stride * 3, B_TRAJ, &od.traj)))
         return rc;
     if ((rc = stage_out(ctx, out->mem, out->traj_hash, n, B_HASH, &od.hash))) return rc;
@@ -311,7 +325,7 @@ int prepare_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, OutDev &od) {
 
 int finish_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od) {
     int rc;
-    if ((rc = copy_back(ctx, out->mem, out->payoff_x2, od.payoff, n))) return rc;
+    if (!od.payoff_direct && (rc = copy_back(ctx, out->mem, out->payoff_x2, od.payoff, n))) return rc;
     if ((rc = copy_back(ctx, out->mem, out->traj, od.traj, n * (uint64_t)out->traj_stride * 3))) return rc;
     if ((rc = copy_back(ctx, out->mem, out->traj_hash, od.hash, n))) return rc;
     if ((rc = copy_back(ctx, out->mem, out->sums, reinterpret_cast<const uint64_t *>(od.sums), (uint64_t)8)))
@@ -759,6 +773,10 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "force_general")) {
         ctx->force_general = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "zero_copy")) {
+        ctx->zero_copy = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "force_warp")) {
