@@ -23,7 +23,12 @@
 
 struct LaneParams {
     WarpParams w;
-    uint32_t words;     /* X[0 .. words) stored per lane; 0 for MoldState */
+    uint32_t words_pad; /* rows X[0 .. words_pad) are produced per lane (multiple of 8, <= 624); 0 for MoldState */
+    uint32_t keep;      /* rows [0, keep) have their own shared-memory row (multiple of 8): X[k-227] operands */
+    uint32_t ring;      /* rows >= keep live in a ring of this many rows (multiple of 8; 0: none, keep = words_pad) */
+    uint32_t ring_m;    /* floor(2^32 / ring) */
+    uint32_t hi0;       /* highest draw index step 0 can read, over the batch */
+    uint32_t hstep;     /* hi of step s+1 - hi of step s = gen + rows cols - 1 + 2 */
     uint32_t dmax;      /* largest depth in the batch */
     uint32_t mulc;      /* 1812433253, passed as data so that it lives in a register: IMAD then takes the
                          * chain index as its immediate addend and a chain step is SHF + LOP3 + IMAD */
@@ -84,15 +89,15 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
     extern __shared__ __align__(16) uint32_t lane_smem[];
     const WarpParams &P = LP.w;
     const int lane = threadIdx.x;
-    uint32_t *col = lane_smem + lane; /* X[k] of this lane's rollout at col[32 k] */
+    uint32_t *col = lane_smem + lane; /* X[k] of this lane's rollout: row k < keep at col[32 k], else in the ring */
     const ModConst m3 = {3u, 1431655765u, 1u};
-    const uint32_t words = LP.words;
-    const uint32_t w2 = words < (uint32_t)MT_LAG ? words : (uint32_t)MT_LAG;
+    const uint32_t words_pad = LP.words_pad, keep = LP.keep, ring = LP.ring;
     const uint32_t mulc = LP.mulc, one = LP.one;
+    uint32_t *const ring_begin = col + 32 * keep, *const ring_end = ring_begin + 32 * ring;
 
     unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_s = 0;
     const uint64_t chunks = (P.n + 31) / 32;
-    /* seeds of the NEXT chunk are fetched one chunk ahead: a warp is alone on its scheduler most of the time */
+    /* seeds of the NEXT chunk are fetched one chunk ahead */
     uint32_t e_nx = 0, l_nx = 0, em_nx = 0, lm_nx = 0;
     auto fetch = [&](uint64_t chunk) {
         if (chunk >= chunks) return;
@@ -121,56 +126,32 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
             bias = P.bias ? P.bias[ii] : P.bias_u;
         }
         const uint64_t soff = (MODE == 0) ? (P.step_off ? P.step_off[ii] : ii * (uint64_t)P.depth_u) : 0;
-        if (KIND == KIND_TREE) {
-            __syncwarp();
-            /* ---- phase 2: X[k], k < 227, from the two chains in lock-step */
-            uint32_t k1 = 1, k398 = 398;
-            uint32_t *dst = col;
-#pragma unroll 8
-            for (uint32_t k = 0; k < w2; ++k) {
-                const uint32_t en = lane_seed_step(e, mulc, k1);
-                *dst = mt_twist_dev(e, en, l);
-                dst += 32;
-                e = en;
-                l = lane_seed_step(l, mulc, k398);
-                k1 = lane_fma_add(k1, one, 1);
-                k398 = lane_fma_add(k398, one, 1);
-            }
-            /* ---- phase 3: X[k], 227 <= k < words <= 623, from the lane's own column */
-#pragma unroll 8
-            for (uint32_t k = MT_LAG; k < words; ++k) {
-                const uint32_t en = lane_seed_step(e, mulc, k1);
-                *dst = mt_twist_dev(e, en, dst[-32 * MT_LAG]);
-                dst += 32;
-                e = en;
-                k1 = lane_fma_add(k1, one, 1);
-            }
-        }
-
-        /* ---- phase 4: play */
-        __syncwarp();
         uint32_t h = PCU_HASH_INIT;
         uint8_t *tr = (P.traj && live) ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
-        uint32_t dloop = d;
-        if (MODE == 1) dloop = LP.dmax; /* the model chains advance in lock-step for every lane */
         uint32_t mk1 = 1, mk398 = 398;
-        for (uint32_t s = 0; s < dloop; ++s) {
-            uint32_t joint;
+
+        /* ---- one step of every rollout of the chunk (phase 4); warp-uniform s */
+        auto play = [&](uint32_t s) {
+            uint32_t joint = 0;
             if (MODE == 0) {
-                joint = P.code_u16 ? (uint32_t)((const uint16_t *)P.codes)[soff + s]
-                                   : (uint32_t)((const uint8_t *)P.codes)[soff + s];
-            } else {
+                if (s < d)
+                    joint = P.code_u16 ? (uint32_t)((const uint16_t *)P.codes)[soff + s]
+                                       : (uint32_t)((const uint8_t *)P.codes)[soff + s];
+            } else { /* the model chains advance in lock-step for every lane */
                 const uint32_t a0 = lane_model_word(em, lm, mk1, mk398, mulc, one);
                 const uint32_t a1 = lane_model_word(em, lm, mk1, mk398, mulc, one);
                 const uint32_t b0 = lane_model_word(em, lm, mk1, mk398, mulc, one);
                 const uint32_t b1 = lane_model_word(em, lm, mk1, mk398, mulc, one);
                 joint = mod64(a0, a1, P.mrow) * P.cols + mod64(b0, b1, P.mcol);
             }
-            if (MODE == 1 && s >= d) continue;
+            if (s >= d) return;
             if (KIND == KIND_TREE) {
                 pos += P.gen_words + joint; /* discard(idx), T == 1: chance action 0 (random-tree.hh:89) */
-                const uint32_t hi = mt_temper(col[32 * pos]);
-                const uint32_t lo = mt_temper(col[32 * pos + 32]);
+                uint32_t q0 = pos, q1 = pos + 1;
+                if (q0 >= keep) q0 = keep + mod32(q0 - keep, ring, LP.ring_m);
+                if (q1 >= keep) q1 = keep + mod32(q1 - keep, ring, LP.ring_m);
+                const uint32_t hi = mt_temper(col[32 * q0]);
+                const uint32_t lo = mt_temper(col[32 * q1]);
                 bias += (int)mod64(hi, lo, m3) - 1; /* :97 */
                 pos += 2;
             }
@@ -181,7 +162,63 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
                 tr[3 * s + 1] = (uint8_t)(joint - r * P.cols);
                 tr[3 * s + 2] = 0;
             }
+        };
+
+        if (KIND == KIND_TREE) {
+            __syncwarp();
+            /* ---- phases 2-3 in blocks of 8 rows; a play step runs as soon as every row it can read exists,
+             * after which the rows below the next step's lowest reachable draw are dead and the ring reuses them */
+            uint32_t k1 = 1, k398 = 398;
+            uint32_t *dst = col;
+            const uint32_t *src3 = col; /* X[k - 227] for phase 3: always a kept row */
+            uint32_t s = 0, hi = LP.hi0; /* hi = highest draw index step s can read, over the whole batch */
+            auto row2 = [&]() { /* X[k], k < 227, from the two chains in lock-step */
+                const uint32_t en = lane_seed_step(e, mulc, k1);
+                *dst = mt_twist_dev(e, en, l);
+                dst += 32;
+                e = en;
+                l = lane_seed_step(l, mulc, k398);
+                k1 = lane_fma_add(k1, one, 1);
+                k398 = lane_fma_add(k398, one, 1);
+            };
+            auto row3 = [&]() { /* X[k], 227 <= k <= 622, from the lane's own kept rows */
+                const uint32_t en = lane_seed_step(e, mulc, k1);
+                *dst = mt_twist_dev(e, en, *src3);
+                dst += 32;
+                src3 += 32;
+                e = en;
+                k1 = lane_fma_add(k1, one, 1);
+            };
+            auto after_block = [&](uint32_t kb) {
+                if (kb + 8 > keep && dst == ring_end) dst = ring_begin;
+                while (s < LP.dmax && hi < kb + 8) {
+                    __syncwarp();
+                    play(s);
+                    ++s;
+                    hi += LP.hstep;
+                }
+            };
+            const uint32_t n2 = words_pad < 224u ? words_pad : 224u;
+            for (uint32_t kb = 0; kb < n2; kb += 8) {
+#pragma unroll
+                for (int r = 0; r < 8; ++r) row2();
+                after_block(kb);
+            }
+            if (words_pad > 224u) {
+                row2(); row2(); row2();                 /* 224..226 */
+                row3(); row3(); row3(); row3(); row3(); /* 227..231 */
+                after_block(224u);
+                for (uint32_t kb = 232; kb < words_pad; kb += 8) {
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) row3();
+                    after_block(kb);
+                }
+            }
+            for (; s < LP.dmax; ++s) play(s); /* not reached when hi0/hstep cover the batch; kept for safety */
+        } else {
+            for (uint32_t s = 0; s < LP.dmax; ++s) play(s);
         }
+
         if (live) {
             uint32_t pay = 0;
             if (KIND == KIND_TREE) pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
@@ -220,22 +257,29 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
 /* Largest draw index any rollout of the batch reads, + 2 (= LaneParams.words), for batches
  * whose positions / depths are per-rollout arrays: pos - gen + d (gen + rows cols - 1 + 2). */
 static __global__ void k_lane_bound(uint64_t n, const uint32_t *pos, uint32_t pos_u, const uint16_t *depth, uint32_t depth_u,
-                             uint32_t gen_words, uint32_t per_step, unsigned long long *out /* [0] words [1] dmax */) {
-    unsigned long long mw = 0, md = 0;
+                             uint32_t gen_words, uint32_t per_step, unsigned long long *out /* [0] words [1] dmax [2] max pos [3] ~min pos */) {
+    unsigned long long mw = 0, md = 0, mp = 0, mq = 0; /* mq = max of ~pos: the smallest position */
     for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
         const unsigned long long p = pos ? pos[i] : pos_u, d = depth ? depth[i] : depth_u;
         const unsigned long long w = p - gen_words + d * per_step;
         mw = w > mw ? w : mw;
         md = d > md ? d : md;
+        mp = p > mp ? p : mp;
+        mq = (0xffffffffull - p) > mq ? (0xffffffffull - p) : mq;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
         const unsigned long long a = __shfl_xor_sync(PCU_FULL, mw, o), b = __shfl_xor_sync(PCU_FULL, md, o);
         mw = a > mw ? a : mw;
         md = b > md ? b : md;
+        const unsigned long long c = __shfl_xor_sync(PCU_FULL, mp, o), e = __shfl_xor_sync(PCU_FULL, mq, o);
+        mp = c > mp ? c : mp;
+        mq = e > mq ? e : mq;
     }
     if ((threadIdx.x & 31) == 0) {
         atomicMax(out + 0, mw);
         atomicMax(out + 1, md);
+        atomicMax(out + 2, mp);
+        atomicMax(out + 3, mq);
     }
 }

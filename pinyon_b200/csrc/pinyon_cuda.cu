@@ -60,6 +60,7 @@ struct pcu_ctx {
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
     int zero_copy = 1; /* payoffs of large batches go straight to pinned host buffers */
+    int lane_full_columns = 0; /* test hook: k_lane keeps every row (no ring) */
     int force_warp = 0; /* test hook: keep distinct-root batches on k_warp instead of k_lane */
     int host_checkpoints = 0; /* test hook: brute-force checkpoints on the host instead of the jump kernels */
     DevBuf buf[B_COUNT];
@@ -617,40 +618,73 @@ int launch_warp(pcu_ctx *ctx, const WarpParams &P0) {
 /* Draw-index bound and largest depth of a batch (k_lane's shared-memory column height).
  * Batch-uniform positions and depths need no kernel. */
 int lane_bound(pcu_ctx *ctx, uint64_t n, const uint32_t *d_pos, uint32_t pos_u, const uint16_t *d_depth,
-               uint32_t depth_u, uint32_t gen_words, uint32_t per_step, uint64_t *words, uint64_t *dmax) {
+               uint32_t depth_u, uint32_t gen_words, uint32_t per_step, uint64_t *words, uint64_t *dmax,
+               uint32_t *pos_min = nullptr, uint32_t *pos_max = nullptr) {
     if (!d_pos && !d_depth) {
         *words = (uint64_t)pos_u - gen_words + (uint64_t)depth_u * per_step;
         *dmax = depth_u;
+        if (pos_min) *pos_min = pos_u;
+        if (pos_max) *pos_max = pos_u;
         return PCU_OK;
     }
-    CU(ctx->buf[B_BOUND].ensure(16));
+    CU(ctx->buf[B_BOUND].ensure(32));
     unsigned long long *o = reinterpret_cast<unsigned long long *>(ctx->buf[B_BOUND].p);
-    CU(cudaMemsetAsync(o, 0, 16, ctx->stream));
+    CU(cudaMemsetAsync(o, 0, 32, ctx->stream));
     uint64_t blocks = std::min<uint64_t>((n + 255) / 256, (uint64_t)ctx->sms * 8);
     k_lane_bound<<<(unsigned)blocks, 256, 0, ctx->stream>>>(n, d_pos, pos_u, d_depth, depth_u, gen_words, per_step, o);
     ctx->launches++;
     CU(cudaGetLastError());
-    unsigned long long h[2];
-    CU(cudaMemcpyAsync(h, o, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    unsigned long long h[4];
+    CU(cudaMemcpyAsync(h, o, 32, cudaMemcpyDeviceToHost, ctx->stream));
     CU(cudaStreamSynchronize(ctx->stream));
     *words = h[0];
     *dmax = h[1];
+    if (pos_max) *pos_max = (uint32_t)h[2];
+    if (pos_min) *pos_min = (uint32_t)(0xffffffffull - h[3]);
     return PCU_OK;
 }
 
-/* k_lane: one warp per CTA, 32 rollouts per pass; shared memory = words x 32 lanes x 4 B. */
+/* k_lane: one warp per CTA, 32 rollouts per pass.  Shared memory = (keep + ring) rows x 32 lanes x 4 B:
+ * rows [0, keep) are the X[k-227] operands of the rows past 227, the ring holds the window of rows between the
+ * lowest draw the next unplayed step can read and the highest one the generation has reached (lane.cuh). */
+struct LaneGeom {
+    uint32_t words = 0, dmax = 0, pos_min = 0, pos_max = 0;
+};
+
 template <int KIND, int MODE>
-int launch_lane(pcu_ctx *ctx, const WarpParams &W, uint32_t words, uint32_t dmax) {
+int launch_lane(pcu_ctx *ctx, const WarpParams &W, const LaneGeom &g) {
     LaneParams LP;
+    memset(&LP, 0, sizeof(LP));
     LP.w = W;
-    LP.words = words;
-    LP.dmax = dmax;
+    LP.dmax = g.dmax;
+    if (KIND == KIND_TREE) {
+        const uint32_t rc1 = W.rows * W.cols - 1, gen = W.gen_words;
+        const uint32_t base_min = g.pos_min - gen, base_max = g.pos_max - gen;
+        LP.words_pad = (g.words + 7) / 8 * 8;
+        LP.hstep = gen + rc1 + 2;
+        LP.hi0 = base_max + gen + rc1 + 1;
+        uint32_t keep = LP.words_pad > MT_LAG ? (LP.words_pad - MT_LAG + 7) / 8 * 8 : 0;
+        uint32_t window = 0;
+        for (uint32_t s = 0; s < g.dmax; ++s) {
+            const uint32_t lo = base_min + (s + 1) * gen + 2 * s, hi = LP.hi0 + s * LP.hstep;
+            if (hi >= keep) window = std::max(window, hi - std::max(lo, keep) + 1);
+        }
+        uint32_t ring = (window + 7 + 7) / 8 * 8;
+        if (ctx->lane_full_columns || keep + ring >= LP.words_pad) {
+            keep = LP.words_pad;
+            ring = 0;
+        }
+        LP.keep = keep;
+        LP.ring = ring;
+        LP.ring_m = ring ? (uint32_t)(0x100000000ull / ring) : 0;
+    }
+    const uint32_t rows = LP.keep + LP.ring;
     LP.mulc = 1812433253u;
     LP.one = 1u;
     CU(ctx->buf[B_L397].ensure(sizeof(uint32_t) * 2 * W.n));
     LP.l397 = reinterpret_cast<uint32_t *>(ctx->buf[B_L397].p);
     LP.lm397 = LP.l397 + W.n;
-    const size_t smem = std::max<size_t>((size_t)words * 32 * 4, 16);
+    const size_t smem = std::max<size_t>((size_t)rows * 32 * 4, 16);
     int per_sm = (int)std::min<size_t>(32, (227 * 1024) / (smem + 1024));
     if (per_sm < 1) per_sm = 1;
     uint64_t blocks = std::min<uint64_t>((W.n + 31) / 32, (uint64_t)ctx->sms * per_sm);
@@ -773,6 +807,10 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "force_general")) {
         ctx->force_general = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "lane_full_columns")) {
+        ctx->lane_full_columns = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "zero_copy")) {
@@ -979,13 +1017,17 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     /* lane-per-rollout kernel: transitions == 1 (draw positions depend on the action codes only) and every
      * read inside the first refill of the state engine; mode P also needs 4 dmax model words below 227 */
     uint64_t lane_words = 0, lane_dmax = 0;
+    LaneGeom geom;
     bool lane = !ctx->force_warp && T == 1;
     if (lane) {
         const uint32_t per_step = gen_words + b->rows * b->cols - 1 + 2;
         if ((rc = lane_bound(ctx, n, d_pos, b->state_pos_u, d_depth, b->depth_u, gen_words, per_step, &lane_words,
-                             &lane_dmax)))
+                             &lane_dmax, &geom.pos_min, &geom.pos_max)))
             return rc;
-        lane = lane_words <= MT_N - 1 && (rng->mode == PCU_MODEL_STREAM || 4 * lane_dmax <= MT_LAG - 3);
+        lane = lane_words <= MT_N - 1 && (rng->mode == PCU_MODEL_STREAM || 4 * lane_dmax <= MT_LAG - 3) &&
+               geom.pos_min >= gen_words;
+        geom.words = (uint32_t)lane_words;
+        geom.dmax = (uint32_t)lane_dmax;
     }
     if (rng->mode == PCU_MODEL_STREAM) {
         uint64_t total_steps = n * (uint64_t)b->depth_u;
@@ -998,7 +1040,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         W.code_u16 = c16;
         ctx->path = lane ? "lane_private_S" : "warp_private_S";
         if (lane)
-            rc = launch_lane<KIND_TREE, 0>(ctx, W, (uint32_t)lane_words, (uint32_t)lane_dmax);
+            rc = launch_lane<KIND_TREE, 0>(ctx, W, geom);
         else
             rc = launch_warp<KIND_TREE, 0>(ctx, W);
         if (rc) return rc;
@@ -1006,7 +1048,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         W.model_seeds = d_mseed;
         ctx->path = lane ? "lane_private_P" : "warp_private_P";
         if (lane)
-            rc = launch_lane<KIND_TREE, 1>(ctx, W, (uint32_t)lane_words, (uint32_t)lane_dmax);
+            rc = launch_lane<KIND_TREE, 1>(ctx, W, geom);
         else
             rc = launch_warp<KIND_TREE, 1>(ctx, W);
         if (rc) return rc;
@@ -1080,7 +1122,9 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         if ((rc = lane_bound(ctx, n, nullptr, 0, d_depth, b->depth_u, 0, 0, &lw, &dmax))) return rc;
         const bool lane = !ctx->force_warp && 4 * dmax <= MT_LAG - 3;
         ctx->path = lane ? "lane_mold_P" : "warp_mold_P";
-        rc = lane ? launch_lane<KIND_MOLD, 1>(ctx, W, 0, (uint32_t)dmax) : launch_warp<KIND_MOLD, 1>(ctx, W);
+        LaneGeom geom;
+        geom.dmax = (uint32_t)dmax;
+        rc = lane ? launch_lane<KIND_MOLD, 1>(ctx, W, geom) : launch_warp<KIND_MOLD, 1>(ctx, W);
         if (rc) return rc;
     }
     return finish_all(ctx, out, n, od, rng);

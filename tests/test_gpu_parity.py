@@ -146,15 +146,17 @@ def test_tree_private_roots_lane(ctx, oracle, mode, shape):
     mseeds = rng.integers(0, 2**63, n).astype(np.uint64) if mode == "P" else None
     exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=1, model_seed=4,
                                       model_pre_discard=9, model_seeds=mseeds, **kw)
-    for force_warp in (0, 1):
+    for force_warp, full in ((0, 0), (0, 1), (1, 0)):
         eng = Engine(4).discard(9)
         ctx.set_option("force_warp", force_warp)
+        ctx.set_option("lane_full_columns", full)  # every row kept vs the ring of live rows
         try:
             got = run_tree(ctx, n, rows=rows, cols=cols, T=1, depth=kw["depth"], state_seed=kw["state_seed"],
                            pre=kw["state_pre_discard"], tseed=kw["transition_seed"], bias=kw["payoff_bias"],
                            engine=None if mode == "P" else eng, model_seeds=mseeds)
         finally:
             ctx.set_option("force_warp", 0)
+            ctx.set_option("lane_full_columns", 0)
         assert ctx.last_path == ("warp_private_" if force_warp else "lane_private_") + mode
         check_same(got, exp, n)
         if mode == "S":
@@ -316,5 +318,48 @@ def test_full_size_properties(ctx, oracle):
                                           want_traj=False)
         assert np.array_equal(payoff[start:start + 4096], exp["payoff"])
         assert np.array_equal(th[start:start + 4096], exp["traj_hash"])
+    ref = Engine(0).discard(40 * n)
+    assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
+
+
+def test_zero_copy_payoffs_equal_staged(ctx):
+    """Batches >= 2^20 into PINNED host buffers are written by the kernels straight over PCIe; pageable
+    buffers take the staged copy.  Same bytes either way, and the option switches it off."""
+    n = (1 << 21) + 12345
+    staged = np.zeros(n, np.uint8)
+    s0 = np.zeros(8, np.uint64)
+    ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, engine=Engine(3), payoff=staged, sums=s0)
+    pinned = ctx.pinned(n, np.uint8)
+    for zero_copy in (1, 0):
+        pinned[:] = 255
+        s1 = np.zeros(8, np.uint64)
+        ctx.set_option("zero_copy", zero_copy)
+        try:
+            ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, engine=Engine(3), payoff=pinned, sums=s1)
+        finally:
+            ctx.set_option("zero_copy", 1)
+        assert np.array_equal(pinned, staged)
+        assert np.array_equal(s0, s1)
+
+
+def test_distinct_roots_full_size_windows(ctx, oracle):
+    """SURVEY 8(d) M1-DR at 2^22: state_seed_i = i; exact counts and sampled windows against the oracle."""
+    n = 1 << 22
+    seeds = np.arange(n, dtype=np.uint64)
+    payoff = np.zeros(n, np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    eng = Engine(0)
+    ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, state_seed=seeds, engine=eng, payoff=payoff, traj_hash=th,
+                            sums=sums)
+    assert ctx.last_path == "lane_private_S"
+    assert int(sums[:3].sum()) == n and int(sums[3]) == 10 * n
+    assert np.bincount(payoff, minlength=3).tolist() == [int(sums[2]), int(sums[1]), int(sums[0])]
+    assert int(th.astype(np.uint64).sum()) == int(sums[4])
+    for start in (0, 1_234_567, n - 2048):
+        exp = loader.random_tree_rollouts(oracle, 2048, rows=3, cols=3, depth=10, model_pre_discard=40 * start,
+                                          state_seed=seeds[start:start + 2048].copy(), want_traj=False)
+        assert np.array_equal(payoff[start:start + 2048], exp["payoff"])
+        assert np.array_equal(th[start:start + 2048], exp["traj_hash"])
     ref = Engine(0).discard(40 * n)
     assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
