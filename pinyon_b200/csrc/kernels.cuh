@@ -188,6 +188,12 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
     uint32_t *xm = mine + (KIND == KIND_TREE ? MT_N : 0);      /* model engine (mode P) */
     const ModConst m10 = {10u, 429496729u, 6u};
     const ModConst m3 = {3u, 1431655765u, 1u};
+    /* fq[n][S] = (double)(float)(n / S) (random-tree.hh:122-133 through math.hh:30-33) behind the engines */
+    double *fq_s = reinterpret_cast<double *>(smem_raw + (((size_t)warps_per_block * MT_N * 4 * (ENGINES ? ENGINES : 1) + 7) & ~(size_t)7));
+    if (KIND == KIND_TREE && P.T > 1) {
+        for (uint32_t k = threadIdx.x; k < 11u * P.fq_w; k += blockDim.x) fq_s[k] = P.fq[k];
+        __syncthreads();
+    }
 
     unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_s = 0;
     const uint64_t warp0 = (uint64_t)blockIdx.x * warps_per_block + wib;
@@ -232,7 +238,12 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
                 c = code - r * P.cols;
             } else {
                 /* lanes 0..3 draw the four model words of this step (monte-carlo-model.hh:89-90) */
-                const uint32_t w = wmt_fetch(em, 4ll * s + lane, lane < 4, lane);
+                const int mrel = (int)(4ll * s - em.base);
+                uint32_t w;
+                if (mrel >= 0 && mrel + 4 <= MT_N) /* the step's four draws lie in the current block */
+                    w = mt_temper(xm[mrel + (lane & 3)]);
+                else
+                    w = wmt_fetch(em, 4ll * s + lane, lane < 4, lane);
                 const ModConst &mc = (lane & 2) ? P.mcol : P.mrow;
                 const uint32_t m = mod32(w, mc.n, mc.m);
                 const uint32_t lo = __shfl_down_sync(PCU_FULL, m, 1);
@@ -248,7 +259,13 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
                 if (T > 1) {
                     /* lanes 0..2T-1 read the 2T words the chosen cell's strategies were drawn
                      * from (random-tree.hh:169); lane k then owns transition k. */
-                    const uint32_t w = wmt_fetch(es, cur + 2ll * st + lane, lane < (int)(2 * T), lane);
+                    const int crel = (int)(cur + 2ll * st - es.base);
+                    uint32_t w = 0;
+                    if (crel >= 0 && crel + 2 * (int)T <= MT_N) { /* the cell's draws lie in the current block */
+                        if (lane < (int)(2 * T)) w = mt_temper(xs[crel + lane]);
+                    } else {
+                        w = wmt_fetch(es, cur + 2ll * st + lane, lane < (int)(2 * T), lane);
+                    }
                     const uint32_t hi = __shfl_sync(PCU_FULL, w, (2 * lane) & 31);
                     const uint32_t lo = __shfl_sync(PCU_FULL, w, (2 * lane + 1) & 31);
                     int nk = 0;
@@ -256,9 +273,7 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
                         nk = (int)mod64(hi, lo, m10) + 1;
                         if (nk * P.thr_q < P.thr_p * 10) nk = 0;
                     }
-                    int S = nk;
-#pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) S += __shfl_xor_sync(PCU_FULL, S, o);
+                    int S = __reduce_add_sync(PCU_FULL, nk);
                     if (S == 0) {
                         if (lane == 0) nk = 1;
                         S = 1;
@@ -266,7 +281,7 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
                     double pp = pu;
                     for (uint32_t k = 0; k < T; ++k) {
                         const int n_k = __shfl_sync(PCU_FULL, nk, k);
-                        pp -= __ldg(P.fq + (uint32_t)n_k * P.fq_w + (uint32_t)S);
+                        pp -= fq_s[(uint32_t)n_k * P.fq_w + (uint32_t)S];
                         if (pp <= 0) {
                             ch = k;
                             break;
@@ -274,7 +289,12 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
                     }
                 }
                 cur += (long long)P.gen_words + st + ch;
-                const uint32_t w = wmt_fetch(es, cur + lane, lane < 2, lane);
+                const int brel = (int)(cur - es.base);
+                uint32_t w;
+                if (brel >= 0 && brel + 2 <= MT_N)
+                    w = mt_temper(xs[brel + (lane & 1)]);
+                else
+                    w = wmt_fetch(es, cur + lane, lane < 2, lane);
                 const uint32_t hi = __shfl_sync(PCU_FULL, w, 0);
                 const uint32_t lo = __shfl_sync(PCU_FULL, w, 1);
                 bias += (int)mod64(hi, lo, m3) - 1;

@@ -560,7 +560,7 @@ template <int KIND, int MODE>
 int launch_warp(pcu_ctx *ctx, const WarpParams &P0) {
     constexpr int ENGINES = (KIND == KIND_TREE ? 1 : 0) + (MODE == 1 ? 1 : 0);
     const int warps = 8;
-    const size_t smem = (size_t)warps * MT_N * 4 * (ENGINES ? ENGINES : 1);
+    const size_t smem = (size_t)warps * MT_N * 4 * (ENGINES ? ENGINES : 1) + 8 + sizeof(double) * 11 * (P0.T > 1 ? P0.fq_w : 0);
     auto kern = k_warp<KIND, MODE>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const uint64_t slab = ENGINES ? std::min<uint64_t>(P0.n, WARP_SLAB) : P0.n;
