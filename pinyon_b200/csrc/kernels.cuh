@@ -107,6 +107,8 @@ struct WarpParams {
     const double *pu_slab;
 };
 
+#include "lane.cuh"
+
 /* A private MT19937 held in shared memory by one warp.  x[] is libstdc++'s state
  * array; base is the draw index of x[0] (-624 while x still holds the seeded array). */
 struct WarpMT {
@@ -176,54 +178,113 @@ __device__ __forceinline__ uint32_t wmt_fetch(WarpMT &e, long long abs, bool act
     return val;
 }
 
+/* Inputs of the small-batch kernel k_small (MODE 2), all passed BY VALUE in the launch parameters so that a
+ * call of <= 32 rollouts is one launch and one synchronisation: the model engine in libstdc++'s form and the
+ * per-rollout state fields.  Replaces Model::inference(State&&, ModelOutput&) (monte-carlo-model.hh:41-56). */
+struct SmallExtra {
+    uint32_t win[MT_N]; /* model engine words */
+    uint32_t win_p;     /* next-word position 0..624 */
+    uint32_t n;
+    uint32_t mulc;      /* 1812433253 as data (lane.cuh) */
+    uint32_t pad;
+    uint64_t state_seed[32], tseed[32];
+    uint32_t pos[32];
+    int32_t bias[32];
+    uint16_t depth[32];
+};
+
+/* MODE 0: mode S, action codes from k_gen_codes2.  MODE 1: mode P, model engines seeded per rollout.
+ * MODE 2: mode S for <= 32 rollouts in ONE CTA (warp w = rollout w): every warp owns a copy of the model
+ * engine and walks it to its rollout's offset; the state engines are seeded in the kernel, lane-per-rollout. */
 template <int KIND, int MODE>
-__global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
+__device__ __forceinline__ void warp_body(const WarpParams &P, const SmallExtra *X) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int wib = threadIdx.x >> 5;
     const int warps_per_block = blockDim.x >> 5;
-    constexpr int ENGINES = (KIND == KIND_TREE ? 1 : 0) + (MODE == 1 ? 1 : 0);
-    uint32_t *mine = reinterpret_cast<uint32_t *>(smem_raw) + (size_t)wib * MT_N * (ENGINES ? ENGINES : 1);
+    constexpr int ENGINES = (KIND == KIND_TREE ? 1 : 0) + (MODE >= 1 ? 1 : 0);
+    /* MODE 2 pads a warp's region by one word: lane r then seeds engine r without bank conflicts */
+    constexpr size_t WSTRIDE = (size_t)MT_N * (ENGINES ? ENGINES : 1) + (MODE == 2 ? 1 : 0);
+    uint32_t *mine = reinterpret_cast<uint32_t *>(smem_raw) + (size_t)wib * WSTRIDE;
     uint32_t *xs = mine;                                       /* state engine */
-    uint32_t *xm = mine + (KIND == KIND_TREE ? MT_N : 0);      /* model engine (mode P) */
+    uint32_t *xm = mine + (KIND == KIND_TREE ? MT_N : 0);      /* model engine (modes P and 2) */
     const ModConst m10 = {10u, 429496729u, 6u};
     const ModConst m3 = {3u, 1431655765u, 1u};
+    double *pu_s = reinterpret_cast<double *>(smem_raw + (((size_t)warps_per_block * WSTRIDE * 4 + 7) & ~(size_t)7));
     /* fq[n][S] = (double)(float)(n / S) (random-tree.hh:122-133 through math.hh:30-33) behind the engines */
-    double *fq_s = reinterpret_cast<double *>(smem_raw + (((size_t)warps_per_block * MT_N * 4 * (ENGINES ? ENGINES : 1) + 7) & ~(size_t)7));
-    if (KIND == KIND_TREE && P.T > 1) {
+    double *fq_s = pu_s + (MODE == 2 ? 32 : 0);
+    if (KIND == KIND_TREE && P.T > 1)
         for (uint32_t k = threadIdx.x; k < 11u * P.fq_w; k += blockDim.x) fq_s[k] = P.fq[k];
-        __syncthreads();
+    if (MODE == 2) {
+        for (int k = lane; k < MT_N; k += 32) xm[k] = X->win[k];
+        if (KIND == KIND_TREE && wib == 0 && lane < (int)X->n) {
+            uint32_t *dst = reinterpret_cast<uint32_t *>(smem_raw) + (size_t)lane * WSTRIDE;
+            uint32_t v = (uint32_t)X->state_seed[lane];
+            dst[0] = v;
+#pragma unroll 8
+            for (uint32_t k = 1; k < MT_N; ++k) {
+                v = lane_seed_step(v, X->mulc, k);
+                dst[k] = v;
+            }
+        }
+        if (KIND == KIND_TREE && P.T > 1 && wib == (warps_per_block > 1 ? 1 : 0) && lane < (int)X->n) {
+            uint32_t v = (uint32_t)X->tseed[lane];
+            const uint32_t t0 = v;
+            uint32_t t1 = 0, t2 = 0, t397 = 0;
+#pragma unroll 8
+            for (uint32_t k = 1; k <= 398; ++k) {
+                v = lane_seed_step(v, X->mulc, k);
+                if (k == 1) t1 = v;
+                if (k == 2) t2 = v;
+                if (k == 397) t397 = v;
+            }
+            pu_s[lane] = prng_uniform_from_words(mt_temper(mt_twist(t0, t1, t397)), mt_temper(mt_twist(t1, t2, v)));
+        }
     }
+    if (MODE == 2 || (KIND == KIND_TREE && P.T > 1)) __syncthreads();
 
     unsigned long long acc_w = 0, acc_d = 0, acc_l = 0, acc_h = 0, acc_s = 0;
     const uint64_t warp0 = (uint64_t)blockIdx.x * warps_per_block + wib;
     const uint64_t stride = (uint64_t)gridDim.x * warps_per_block;
 
     for (uint64_t i = P.i0 + warp0; i < P.i1; i += stride) {
-        const uint32_t d = P.depth ? P.depth[i] : P.depth_u;
-        /* ---- the seeded engines of this rollout, 20 coalesced 128-byte reads each */
-        __syncwarp();
-        if (KIND == KIND_TREE) {
-            const uint32_t *src = P.xs_slab + (i - P.i0) * MT_N;
-#pragma unroll 5
-            for (int k = lane; k < MT_N; k += 32) xs[k] = src[k];
-        }
-        if (MODE == 1) {
-            const uint32_t *src = P.xm_slab + (i - P.i0) * MT_N;
-#pragma unroll 5
-            for (int k = lane; k < MT_N; k += 32) xm[k] = src[k];
-        }
+        uint32_t d;
         double pu = 0.0;
-        if (KIND == KIND_TREE && P.T > 1) pu = P.pu_slab[i - P.i0];
-        __syncwarp();
+        long long moff = 0; /* MODE 2: model draws consumed by the rollouts before this one */
+        if (MODE == 2) {
+            d = X->depth[i];
+            for (uint32_t j = 0; j < (uint32_t)i; ++j) moff += 4ll * X->depth[j];
+            if (KIND == KIND_TREE && P.T > 1) pu = pu_s[i];
+        } else {
+            d = P.depth ? P.depth[i] : P.depth_u;
+            /* ---- the seeded engines of this rollout, 20 coalesced 128-byte reads each */
+            __syncwarp();
+            if (KIND == KIND_TREE) {
+                const uint32_t *src = P.xs_slab + (i - P.i0) * MT_N;
+#pragma unroll 5
+                for (int k = lane; k < MT_N; k += 32) xs[k] = src[k];
+            }
+            if (MODE == 1) {
+                const uint32_t *src = P.xm_slab + (i - P.i0) * MT_N;
+#pragma unroll 5
+                for (int k = lane; k < MT_N; k += 32) xm[k] = src[k];
+            }
+            if (KIND == KIND_TREE && P.T > 1) pu = P.pu_slab[i - P.i0];
+            __syncwarp();
+        }
         WarpMT es = {xs, -(long long)MT_N};
-        WarpMT em = {xm, -(long long)MT_N};
+        WarpMT em = {xm, MODE == 2 ? -(long long)X->win_p : -(long long)MT_N};
 
         long long cur = 0;
         int bias = 0;
         if (KIND == KIND_TREE) {
-            cur = (long long)(P.state_pos ? P.state_pos[i] : P.state_pos_u) - (long long)P.gen_words;
-            bias = P.bias ? P.bias[i] : P.bias_u;
+            if (MODE == 2) {
+                cur = (long long)X->pos[i] - (long long)P.gen_words;
+                bias = X->bias[i];
+            } else {
+                cur = (long long)(P.state_pos ? P.state_pos[i] : P.state_pos_u) - (long long)P.gen_words;
+                bias = P.bias ? P.bias[i] : P.bias_u;
+            }
         }
         const uint64_t soff = (MODE == 0) ? (P.step_off ? P.step_off[i] : i * (uint64_t)P.depth_u) : 0;
         uint32_t h = PCU_HASH_INIT;
@@ -238,12 +299,12 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
                 c = code - r * P.cols;
             } else {
                 /* lanes 0..3 draw the four model words of this step (monte-carlo-model.hh:89-90) */
-                const int mrel = (int)(4ll * s - em.base);
+                const int mrel = (int)(moff + 4ll * s - em.base);
                 uint32_t w;
                 if (mrel >= 0 && mrel + 4 <= MT_N) /* the step's four draws lie in the current block */
                     w = mt_temper(xm[mrel + (lane & 3)]);
                 else
-                    w = wmt_fetch(em, 4ll * s + lane, lane < 4, lane);
+                    w = wmt_fetch(em, moff + 4ll * s + lane, lane < 4, lane);
                 const ModConst &mc = (lane & 2) ? P.mcol : P.mrow;
                 const uint32_t m = mod32(w, mc.n, mc.m);
                 const uint32_t lo = __shfl_down_sync(PCU_FULL, m, 1);
@@ -335,7 +396,22 @@ __global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
     }
 }
 
-#include "lane.cuh"
+template <int KIND, int MODE>
+__global__ void __launch_bounds__(256) k_warp(const WarpParams P) {
+    warp_body<KIND, MODE>(P, nullptr);
+}
+
+struct SmallParams {
+    WarpParams w;
+    SmallExtra x;
+};
+
+/* <= 32 rollouts, mode S, everything in the launch parameters: one launch, no copies in. */
+template <int KIND>
+__global__ void __launch_bounds__(1024) k_small(const __grid_constant__ SmallParams SP) {
+    warp_body<KIND, 2>(SP.w, &SP.x);
+}
+
 #include "seed.cuh"
 
 /* ------------------------------------------------------- integer-issue peak probe */

@@ -38,6 +38,7 @@ struct DevBuf {
     }
 };
 
+constexpr size_t PIN_OUT_BYTES = 32768, PIN_OUT_HASH = 64, PIN_OUT_TRAJ = 256;
 constexpr int PIN_BASE_WINDOW = 1024; /* word offset in pin_small of the staged base window */
 
 enum BufId {
@@ -59,6 +60,8 @@ struct pcu_ctx {
     uint64_t launches = 0;
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
+    int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
+    uint8_t *pin_out = nullptr; /* pinned staging for k_small's outputs (PIN_OUT_BYTES) */
     int zero_copy = 1; /* payoffs of large batches go straight to pinned host buffers */
     int lane_full_columns = 0; /* test hook: k_lane keeps every row (no ring) */
     int force_warp = 0; /* test hook: keep distinct-root batches on k_warp instead of k_lane */
@@ -702,6 +705,63 @@ int launch_lane(pcu_ctx *ctx, const WarpParams &W, const LaneGeom &g) {
     return PCU_OK;
 }
 
+/* <= 32 rollouts in mode S with host buffers: ONE launch whose parameters carry the model engine and the
+ * per-rollout fields, outputs written to pinned staging, the host engine advanced on the CPU while the kernel
+ * runs.  This is Model::inference(State&&, ModelOutput&) (monte-carlo-model.hh:41-56) as TreeBandit calls it. */
+template <int KIND>
+int run_small(pcu_ctx *ctx, SmallParams &SP, uint32_t n, pcu_model_rng *rng, const pcu_out *out) {
+    if (!ctx->pin_out) CU(cudaMallocHost(reinterpret_cast<void **>(&ctx->pin_out), PIN_OUT_BYTES));
+    constexpr size_t ENG = (KIND == KIND_TREE ? 1 : 0) + 1;
+    const size_t wstride = MT_N * ENG + 1;
+    const bool tab = KIND == KIND_TREE && SP.w.T > 1;
+    const size_t smem = ((n * wstride * 4 + 7) & ~(size_t)7) + 32 * sizeof(double) + (tab ? sizeof(double) * 11 * SP.w.fq_w : 0);
+    auto kern = k_small<KIND>;
+    static bool attr_set[2] = {false, false};
+    if (!attr_set[KIND]) {
+        CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_set[KIND] = true;
+    }
+    SP.x.n = n;
+    SP.x.mulc = 1812433253u;
+    memcpy(SP.x.win, rng->mt_x, sizeof(uint32_t) * MT_N);
+    SP.x.win_p = *rng->mt_p;
+    SP.w.n = n;
+    SP.w.i0 = 0;
+    SP.w.i1 = n;
+    SP.w.payoff = ctx->pin_out;
+    SP.w.traj_hash = reinterpret_cast<uint32_t *>(ctx->pin_out + PIN_OUT_HASH);
+    SP.w.traj = out->traj ? ctx->pin_out + PIN_OUT_TRAJ : nullptr;
+    SP.w.traj_stride = out->traj_stride;
+    SP.w.sums = nullptr;
+    kern<<<1, 32 * n, smem, ctx->stream>>>(SP);
+    ctx->launches++;
+    ctx->ev_valid = false;
+    CU(cudaGetLastError());
+    /* the host engine moves on while the kernel runs: 4 draws per step (monte-carlo-model.hh:89-90) */
+    uint64_t steps = 0;
+    for (uint32_t i = 0; i < n; ++i) steps += SP.x.depth[i];
+    int rc = pcu_mt_discard(rng->mt_x, rng->mt_p, 4 * steps);
+    CU(cudaStreamSynchronize(ctx->stream));
+    if (rc) return rc;
+    const uint32_t *hash = reinterpret_cast<const uint32_t *>(ctx->pin_out + PIN_OUT_HASH);
+    if (out->payoff_x2) memcpy(out->payoff_x2, ctx->pin_out, n);
+    if (out->traj_hash) memcpy(out->traj_hash, hash, sizeof(uint32_t) * n);
+    if (out->traj) memcpy(out->traj, ctx->pin_out + PIN_OUT_TRAJ, (size_t)n * out->traj_stride * 3);
+    if (out->sums) {
+        uint64_t sm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (uint32_t i = 0; i < n; ++i) {
+            if (KIND == KIND_TREE)
+                sm[2 - ctx->pin_out[i]] += 1; /* payoff_x2 2 = row win, 1 = draw, 0 = row loss */
+            else
+                sm[1] += 1;
+            sm[4] += hash[i];
+        }
+        sm[3] = steps;
+        memcpy(out->sums, sm, sizeof(sm));
+    }
+    return PCU_OK;
+}
+
 int check_common(pcu_ctx *ctx, const void *batch, const pcu_model_rng *rng, const pcu_out *out) {
     if (!ctx) return PCU_ERR_INVALID;
     if (!batch || !rng || !out) return fail(ctx, PCU_ERR_INVALID, "null batch, rng or out");
@@ -774,6 +834,7 @@ void pcu_destroy(pcu_ctx *ctx) {
     for (auto &b : ctx->buf) b.release();
     ctx->jump.release();
     if (ctx->pin_small) cudaFreeHost(ctx->pin_small);
+    if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
@@ -811,6 +872,10 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "lane_full_columns")) {
         ctx->lane_full_columns = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "small_path")) {
+        ctx->small_path = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "zero_copy")) {
@@ -902,6 +967,30 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     if (out->traj && out->traj_stride < (b->depth ? 1u : b->depth_u))
         return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
     CU(cudaSetDevice(ctx->device));
+    if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST &&
+        rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
+        static thread_local SmallParams SP; /* ~3.6 KB: kept off the stack of recursive searches */
+        memset(&SP.w, 0, sizeof(SP.w));
+        SP.w.rows = b->rows;
+        SP.w.cols = b->cols;
+        SP.w.T = T;
+        SP.w.gen_words = gen_words;
+        SP.w.mrow = make_mod_const(b->rows);
+        SP.w.mcol = make_mod_const(b->cols);
+        SP.w.thr_p = b->thr_p;
+        SP.w.thr_q = b->thr_q;
+        if (T > 1 && (rc = upload_fq(ctx, T, &SP.w.fq, &SP.w.fq_w))) return rc;
+        for (uint32_t i = 0; i < n; ++i) {
+            SP.x.state_seed[i] = b->state_seed ? b->state_seed[i] : b->state_seed_u;
+            SP.x.tseed[i] = b->transition_seed ? b->transition_seed[i] : b->transition_seed_u;
+            SP.x.pos[i] = b->state_pos ? b->state_pos[i] : b->state_pos_u;
+            SP.x.bias[i] = b->payoff_bias ? b->payoff_bias[i] : b->payoff_bias_u;
+            SP.x.depth[i] = b->depth ? b->depth[i] : b->depth_u;
+            if (SP.x.pos[i] < gen_words) return fail(ctx, PCU_ERR_INVALID, "a state_pos is below 2*rows*cols*transitions");
+        }
+        ctx->path = "small_tree";
+        return run_small<KIND_TREE>(ctx, SP, (uint32_t)n, rng, out);
+    }
     OutDev od;
     if ((rc = prepare_out(ctx, out, n, od))) return rc;
     if (n == 0) return finish_all(ctx, out, n, od, rng);
@@ -1067,6 +1156,18 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
     const uint64_t n = b->n;
     CU(cudaSetDevice(ctx->device));
+    if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST &&
+        rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
+        static thread_local SmallParams SP;
+        memset(&SP.w, 0, sizeof(SP.w));
+        SP.w.rows = SP.w.cols = b->n_actions;
+        SP.w.T = 1;
+        SP.w.mrow = make_mod_const(b->n_actions);
+        SP.w.mcol = make_mod_const(b->n_actions);
+        for (uint32_t i = 0; i < n; ++i) SP.x.depth[i] = b->depth ? b->depth[i] : b->depth_u;
+        ctx->path = "small_mold";
+        return run_small<KIND_MOLD>(ctx, SP, (uint32_t)n, rng, out);
+    }
     OutDev od;
     if ((rc = prepare_out(ctx, out, n, od))) return rc;
     if (n == 0) return finish_all(ctx, out, n, od, rng);

@@ -61,11 +61,52 @@ def test_tree_shared_root_stream(ctx, oracle, case, n):
                                       state_seed=sseed, state_pre_discard=pre, transition_seed=tseed, payoff_bias=bias,
                                       model_seed=mseed, model_pre_discard=mpre)
     eng = Engine(mseed).discard(mpre)
-    got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
-                   bias=bias, engine=eng)
+    ctx.set_option("small_path", 0)  # n = 1 through the fused kernel too; the one-launch path has its own test
+    try:
+        got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
+                       bias=bias, engine=eng)
+    finally:
+        ctx.set_option("small_path", 1)
     assert ctx.last_path == "stream_table"
     check_same(got, exp, n)
     assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("n", [1, 2, 32])
+def test_tree_small_batches_one_launch(ctx, oracle, case, n):
+    """<= 32 rollouts from host memory in mode S (what TreeBandit's single-leaf inference does,
+    monte-carlo-model.hh:41-56): ONE k_small launch, engine and state fields in the launch parameters."""
+    rows, cols, T, thr, depth, sseed, pre, tseed, bias, mseed, mpre = case
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth,
+                                      state_seed=sseed, state_pre_discard=pre, transition_seed=tseed, payoff_bias=bias,
+                                      model_seed=mseed, model_pre_discard=mpre)
+    eng = Engine(mseed).discard(mpre)
+    before = ctx.launches
+    got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
+                   bias=bias, engine=eng)
+    assert ctx.last_path == "small_tree" and ctx.launches == before + 1
+    check_same(got, exp, n)
+    assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
+
+
+def test_tree_small_batch_private_ragged(ctx, oracle):
+    """The one-launch path with everything per rollout: seeds, positions, depths, biases, T > 1."""
+    rng = np.random.default_rng(77)
+    n = 29
+    kw = dict(state_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+              state_pre_discard=rng.integers(0, 3000, n).astype(np.uint32),
+              transition_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+              depth=rng.integers(1, 40, n).astype(np.uint32),
+              payoff_bias=rng.integers(-2, 3, n).astype(np.int32))
+    exp = loader.random_tree_rollouts(oracle, n, rows=5, cols=4, transitions=3, thr=(3, 10), model_seed=8,
+                                      model_pre_discard=600, **kw)
+    eng = Engine(8).discard(600)
+    got = run_tree(ctx, n, rows=5, cols=4, T=3, thr=(3, 10), depth=kw["depth"], state_seed=kw["state_seed"],
+                   pre=kw["state_pre_discard"], tseed=kw["transition_seed"], bias=kw["payoff_bias"], engine=eng)
+    assert ctx.last_path == "small_tree"
+    check_same(got, exp, n)
+    assert engine_matches(eng, 8, 600 + 4 * int(kw["depth"].sum()), oracle)
 
 
 def test_tree_known_answers_appendix_b(ctx):
@@ -203,7 +244,7 @@ def test_mold_stream(ctx, oracle, n_actions, depth, n):
     sums = np.zeros(8, np.uint64)
     ctx.rollout_mold(n, n_actions=n_actions, depth=depth, engine=eng, payoff=payoff, traj=traj, traj_stride=depth,
                      traj_hash=th, sums=sums)
-    assert ctx.last_path == "stream_mold"
+    assert ctx.last_path == ("small_mold" if n <= 32 else "stream_mold")
     assert not payoff.any()  # MoldState never sets a payoff: (0, 0)
     assert np.array_equal(traj, exp["traj"])
     assert np.array_equal(th, exp["traj_hash"])
