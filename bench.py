@@ -41,6 +41,12 @@ WORKLOADS = {
     # chain 397*3 + lock-step 227*(3+3+5) + tail 56*(3+5) + play 10*45.
     "tree_d10_3x3x1_dr": dict(kind="tree", rows=3, cols=3, T=1, depth=10, log2n=24, ops_step=318.0, ops_setup=2492.0,
                               ops_exec=458.6, dr=True, kernel="k_lane_pre + k_lane<TREE,S>"),
+    # config B with distinct roots and distinct transition seeds -> k_seed_pre + k_warp (private
+    # 624-word engines refilled ~19.5 times per rollout).  2^20 rollouts per GPU (the CPU needs ~0.3 ms per rollout).
+    # ops_setup = 2492 (state seeding) + 1592 (transition prng); ops_exec per rollout = 430 warp instructions per step
+    # x 32 lanes x 20 steps (ncu r1e) is what the kernel issues, most of it the refills.
+    "tree_d20_9x9x3_dr": dict(kind="tree", rows=9, cols=9, T=3, depth=20, log2n=20, ops_step=4920.0, ops_setup=4084.0,
+                              ops_exec=12800.0, dr=True, kernel="k_seed_pre + k_warp<TREE,S>"),
     "mold_2_10": dict(kind="mold", rows=2, cols=2, T=1, depth=10, log2n=24, ops_step=104.0, ops_exec=70.0,
                       kernel="k_stream2<MOLD,u8>"),
 }
@@ -406,17 +412,16 @@ def run_ours(args, w):
         h2d = 624 * 4 + 8
         if w.get("dr"):
             hbm_bytes = float(n) * (1 + 8 + depth + 8)  # payoff + state seed + action codes + x[397] write/read
-            h2d += 8 * n  # state seeds (transition seeds are not staged when transitions == 1)
+            h2d += 8 * n * (2 if w["T"] > 1 else 1)  # state seeds (+ transition seeds when transitions > 1)
         note = ("achieved = algorithmic int32 ops (SURVEY.md 8(d): %.0f per rollout-step, counted for a PRIVATE state "
                 "stream) / the rollout kernel's own CUDA-event time; peak = int-issue microbenchmark measured in this "
                 "run (LOP3 only %.1f, LOP3:IMAD 1:1 %.1f Gop/s). " % (w["ops_step"], int_peak_alu / 1e9, int_peak / 1e9))
         if w.get("dr"):
             note += ("DISTINCT-ROOT run: every rollout seeds and advances its own state engine (+%.0f ops per rollout "
-                     "for the seeding chain, included in achieved); `executed` counts the %.0f ops per rollout the "
-                     "lane kernels really issue (only the first-refill words a rollout can reach are twisted). "
-                     "kernel_ms brackets k_lane_pre + k_lane; the model-stream code generator (k_gen_codes2 + "
-                     "jump-ahead) runs before it and is in ms_per_step only"
-                     % (w["ops_setup"], w["ops_exec"] * depth))
+                     "for the seeding chains, included in achieved); `executed` counts the %.0f ops per rollout the "
+                     "kernels really issue. kernel_ms brackets the seeding pre-kernel + the rollout kernel (%s); the "
+                     "model-stream code generator (k_gen_codes2 + jump-ahead) runs before it and is in ms_per_step only"
+                     % (w["ops_setup"], w["ops_exec"] * depth, w["kernel"]))
         else:
             note += ("SHARED-STREAM run: every rollout of the batch shares the root's state seed, so the kernel serves "
                      "the state stream from a shared-memory table and only has to generate the model stream: "

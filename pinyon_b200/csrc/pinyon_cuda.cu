@@ -61,6 +61,7 @@ struct pcu_ctx {
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
     int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
+    bool small_attr[2] = {false, false};
     uint8_t *pin_out = nullptr; /* pinned staging for k_small's outputs (PIN_OUT_BYTES) */
     int zero_copy = 1; /* payoffs of large batches go straight to pinned host buffers */
     int lane_full_columns = 0; /* test hook: k_lane keeps every row (no ring) */
@@ -716,10 +717,9 @@ int run_small(pcu_ctx *ctx, SmallParams &SP, uint32_t n, pcu_model_rng *rng, con
     const bool tab = KIND == KIND_TREE && SP.w.T > 1;
     const size_t smem = ((n * wstride * 4 + 7) & ~(size_t)7) + 32 * sizeof(double) + (tab ? sizeof(double) * 11 * SP.w.fq_w : 0);
     auto kern = k_small<KIND>;
-    static bool attr_set[2] = {false, false};
-    if (!attr_set[KIND]) {
+    if (!ctx->small_attr[KIND]) { /* per context: the attribute belongs to this device's copy of the kernel */
         CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set[KIND] = true;
+        ctx->small_attr[KIND] = true;
     }
     SP.x.n = n;
     SP.x.mulc = 1812433253u;
