@@ -33,9 +33,10 @@ extern "C" {
 #define PCU_VERSION 100
 
 #define PCU_OK 0
-#define PCU_ERR_INVALID (-1)     /* bad argument (null pointer, depth 0, T > 9, rows*cols > 65535, ...) */
+#define PCU_ERR_INVALID (-1)     /* bad argument (null pointer, depth 0, rows or cols > 255, ...) */
 #define PCU_ERR_CUDA (-2)        /* a CUDA runtime call failed */
-#define PCU_ERR_UNSUPPORTED (-3) /* legal in Pinyon but outside what the device path reproduces */
+#define PCU_ERR_UNSUPPORTED (-3) /* legal in Pinyon but outside what the device path reproduces (transitions > 8: the
+                                  * reference's Rational<int> arithmetic overflows int there, random-tree.hh:165-184) */
 #define PCU_ERR_NOMEM (-4)
 
 /* Where the array pointers of a batch / output live. */

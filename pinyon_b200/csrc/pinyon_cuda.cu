@@ -425,6 +425,15 @@ int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t sm
 
 constexpr size_t SMEM_LIMIT = 200 * 1024;
 
+/* Whether the fused kernel's per-generator code queue (two buffers of 32 rollouts x depth codes) fits in shared
+ * memory; deeper batches take the general path (codes through HBM). */
+bool stream_fits(uint32_t depth, uint64_t actions) {
+    uint64_t qlen = 1024;
+    while (qlen < 2ull * 32 * depth + 2 * GW_PASS_STEPS) qlen <<= 1;
+    const size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + (size_t)GW_PAIRS * (qlen + 16) * (actions <= 256 ? 1 : 2) + 16;
+    return smem <= SMEM_LIMIT;
+}
+
 /* Fused path (mode S, uniform depth, shared or absent state stream). */
 template <int KIND>
 int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od) {
@@ -954,8 +963,11 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     if (b->mem != out->mem) return fail(ctx, PCU_ERR_INVALID, "batch and out must share a memory space");
     if (b->rows < 1 || b->cols < 1 || b->rows > 255 || b->cols > 255)
         return fail(ctx, PCU_ERR_INVALID, "rows/cols must be 1..255");
-    if (b->transitions < 1 || b->transitions > 9)
-        return fail(ctx, PCU_ERR_INVALID, "transitions must be 1..9 (Rational<int> overflows beyond, SURVEY App. C6)");
+    if (b->transitions < 1) return fail(ctx, PCU_ERR_INVALID, "transitions must be >= 1");
+    if (b->transitions > 8)
+        return fail(ctx, PCU_ERR_UNSUPPORTED,
+                    "transitions > 8: the reference's Rational<int> sum p/10^T (random-tree.hh:165-184, rational.hh:82-87) "
+                    "overflows int once 10^(T-1) * sum(n_k) >= 2^31, so its results are undefined behaviour there");
     if (b->thr_q <= 0 || b->thr_p < 0) return fail(ctx, PCU_ERR_INVALID, "chance_threshold must be p/q with p >= 0, q > 0");
     if (!b->depth && b->depth_u == 0)
         return fail(ctx, PCU_ERR_INVALID, "depth_bound 0 never terminates in the reference (random-tree.hh:95-99)");
@@ -1014,7 +1026,8 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
 
     /* ---- fused path: mode S, uniform depth, one shared state stream, host-visible positions */
     bool fused = !ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && !b->state_seed &&
-                 (T == 1 || !b->transition_seed) && (!b->state_pos || b->mem == PCU_MEM_HOST);
+                 (T == 1 || !b->transition_seed) && (!b->state_pos || b->mem == PCU_MEM_HOST) &&
+                 stream_fits(b->depth_u, (uint64_t)b->rows * b->cols);
     uint32_t pos_min = b->state_pos_u, pos_max = b->state_pos_u;
     if (fused && b->state_pos) {
         pos_min = 0xffffffffu;
@@ -1177,7 +1190,8 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
 
-    if (!ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && b->depth_u > 0) {
+    if (!ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && b->depth_u > 0 &&
+        stream_fits(b->depth_u, (uint64_t)b->n_actions * b->n_actions)) {
         Stream2Params P;
         memset(&P, 0, sizeof(P));
         P.n = n;

@@ -48,7 +48,7 @@ CASES = [
     (2, 2, 2, (1, 2), 5, 7, 13, 1, 1, 99, 7),
     (4, 7, 4, (3, 10), 9, 12345678901234, 700, 0xDEADBEEFCAFE, -2, 2**32 + 5, 1001),
     (1, 1, 1, (0, 1), 1, 5, 0, 0, 0, 1, 623),
-    (5, 2, 9, (1, 1), 3, 99, 0, 3, 0, 3, 624),
+    (5, 2, 8, (1, 1), 3, 99, 0, 3, 0, 3, 624),
     (16, 17, 1, (0, 1), 6, 3, 0, 0, 0, 3, 2),  # rows*cols > 256 -> 16-bit action codes
 ]
 
@@ -331,7 +331,7 @@ def test_empty_and_invalid(ctx):
     before = eng.x.copy()
     ctx.rollout_random_tree(0, rows=3, cols=3, depth=10, engine=eng, sums=sums)
     assert not sums.any() and np.array_equal(eng.x, before)
-    for bad in (dict(rows=3, cols=3, depth=0), dict(rows=0, cols=3, depth=1), dict(rows=3, cols=3, depth=1, transitions=10),
+    for bad in (dict(rows=3, cols=3, depth=0), dict(rows=0, cols=3, depth=1), dict(rows=3, cols=3, depth=1, transitions=0),
                 dict(rows=3, cols=3, depth=2, state_pos=3)):
         with pytest.raises(PcuError) as e:
             ctx.rollout_random_tree(4, engine=Engine(0), **bad)
@@ -404,3 +404,46 @@ def test_distinct_roots_full_size_windows(ctx, oracle):
         assert np.array_equal(th[start:start + 2048], exp["traj_hash"])
     ref = Engine(0).discard(40 * n)
     assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
+
+
+@pytest.mark.parametrize("shape", [
+    (255, 255, 1, (0, 1), 3),    # largest action sets: joint codes need 16 bits, one step is 195 076 state draws
+    (2, 2, 8, (0, 1), 12),       # most chance transitions before the reference's Rational<int> sum overflows int
+    (3, 3, 8, (1, 1), 8),        # threshold 1: only n_k = 10 survives, frequent all-zero rows -> n_0 = 1 fallback
+    (1, 1, 1, (0, 1), 300),      # one action each: the model still draws four words per step
+])
+@pytest.mark.parametrize("distinct", [False, True])
+def test_tree_extreme_shapes(ctx, oracle, shape, distinct):
+    rows, cols, T, thr, depth = shape
+    n = 33  # just above the one-launch path
+    kw = {}
+    if distinct:
+        kw = dict(state_seed=np.arange(n, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15),
+                  transition_seed=np.arange(n, dtype=np.uint64) + np.uint64(2**40))
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth, model_seed=11,
+                                      **kw)
+    eng = Engine(11)
+    got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, engine=eng,
+                   state_seed=kw.get("state_seed", 0), tseed=kw.get("transition_seed", 0))
+    check_same(got, exp, n)
+    assert engine_matches(eng, 11, 4 * depth * n, oracle)
+
+
+def test_mold_deep(ctx, oracle):
+    """MoldState far deeper than one engine refill per rollout (tests/cart/node.cc uses depth 50)."""
+    n, depth = 40, 3000
+    exp = loader.mold_rollouts(oracle, n, n_actions=5, depth=depth, model_seed=2, want_traj=False)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    eng = Engine(2)
+    ctx.rollout_mold(n, n_actions=5, depth=depth, engine=eng, traj_hash=th, sums=sums)
+    assert np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
+    assert engine_matches(eng, 2, 4 * depth * n, oracle)
+
+
+def test_nine_transitions_are_refused(ctx):
+    """random-tree.hh:165-184 sums n_k/10 as Rational<int> over 10^T: the numerator overflows int from T = 9 on
+    (10^8 * sum(n_k) >= 2^31 when sum >= 22), so the reference's results are undefined behaviour; the library says so."""
+    with pytest.raises(PcuError) as e:
+        ctx.rollout_random_tree(64, rows=2, cols=2, transitions=9, depth=3, engine=Engine(0), payoff=np.zeros(64, np.uint8))
+    assert e.value.code == -3
