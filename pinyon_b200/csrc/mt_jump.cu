@@ -39,19 +39,20 @@ __global__ void __launch_bounds__(GEN_THREADS) k_jump_extend(const uint32_t *ck,
 /* window_c[j] = XOR over set coefficients i of g_c of ext[i + j], j = 0..623.
  *
  * The extended sequence (82 KB) and g_c's bitmap sit in shared memory.  A thread owns
- * JA_OUT = 13 CONSECUTIVE outputs (48 threads cover 624; stride 13 is odd, so the 48 loads
- * of one instruction hit distinct banks) and walks the bitmap one 32-bit word at a time:
- * 44 loads give it ext[32w + j0 .. 32w + j0 + 43], after which every set bit k of the word is
- * 13 register XORs with static indices.  The bitmap word is the same for the whole warp, so
+ * JA_OUT = 10 CONSECUTIVE outputs (63 threads cover 624; the loads of one instruction are 2-way bank
+ * conflicted at stride 10, which the idle LSU pipe absorbs) and walks the bitmap one 32-bit word at a time:
+ * 41 loads give it ext[32w + j0 .. 32w + j0 + 40], after which every set bit k of the word is
+ * 10 register XORs with static indices.  The bitmap word is the same for the whole warp, so
  * the per-bit branch is warp-uniform.  The 624 bitmap words are split over `splits` CTAs x SEGS
  * two-warp segments; segments are folded through shared memory, CTAs through atomicXor. */
-constexpr int JA_OUT = 13;
-constexpr int JA_ACTIVE = MT_N / JA_OUT; /* 48 */
+constexpr int JA_OUT = 10;
+constexpr int JA_ACTIVE = (MT_N + JA_OUT - 1) / JA_OUT; /* 63 of the segment's 64 lanes (r1g: 13 x 48 left a quarter idle) */
 constexpr int JA_SEG_THREADS = 64;
 constexpr int JA_SEGS = 8;
 constexpr int JA_EXT_WORDS = 20608; /* >= 32 * 623 + 13 * 47 + 44, multiple of 4 */
 static_assert(JA_EXT_WORDS <= MTJ_EXT_LEN, "extension too short");
-static_assert(JA_ACTIVE * JA_OUT == MT_N, "outputs must tile the window");
+static_assert(JA_ACTIVE * JA_OUT >= MT_N && JA_ACTIVE <= JA_SEG_THREADS, "outputs must cover the window");
+static_assert(JA_EXT_WORDS >= 32 * (MT_N - 1) + JA_OUT * (JA_ACTIVE - 1) + 32 + JA_OUT - 1, "extension too short for the last lane");
 constexpr size_t JA_SMEM = sizeof(uint32_t) * (JA_EXT_WORDS + MTJ_POLY_WORDS + JA_SEGS * MT_N);
 
 __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
@@ -89,15 +90,23 @@ __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
 #pragma unroll
             for (int k = 0; k < 32 + JA_OUT - 1; ++k) r[k] = p[k];
 #pragma unroll
-            for (int k = 0; k < 32; ++k) {
-                if (pw & (1u << k)) {
+            for (int k = 0; k < 32; k += 2) { /* two coefficients at a time: both set is ONE three-input LOP3 per output */
+                const uint32_t two = (pw >> k) & 3u;
+                if (two == 3u) {
+#pragma unroll
+                    for (int m = 0; m < JA_OUT; ++m) acc[m] ^= r[k + m] ^ r[k + 1 + m];
+                } else if (two == 1u) {
 #pragma unroll
                     for (int m = 0; m < JA_OUT; ++m) acc[m] ^= r[k + m];
+                } else if (two == 2u) {
+#pragma unroll
+                    for (int m = 0; m < JA_OUT; ++m) acc[m] ^= r[k + 1 + m];
                 }
             }
         }
 #pragma unroll
-        for (int m = 0; m < JA_OUT; ++m) sred[seg * MT_N + JA_OUT * t + m] = acc[m];
+        for (int m = 0; m < JA_OUT; ++m)
+            if (JA_OUT * t + m < MT_N) sred[seg * MT_N + JA_OUT * t + m] = acc[m];
     }
     __syncthreads();
     for (int j = tid; j < MT_N; j += JA_SEGS * JA_SEG_THREADS) {
