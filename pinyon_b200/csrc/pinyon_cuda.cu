@@ -60,6 +60,7 @@ struct pcu_ctx {
     uint64_t launches = 0;
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
+    int stream3 = 0;    /* fused path: k_stream3 (five role warps per stream) instead of k_stream2; measured slower (1.20 vs 1.11 ms) */
     int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
     bool small_attr[2] = {false, false};
     uint8_t *pin_out = nullptr; /* pinned staging for k_small's outputs (PIN_OUT_BYTES) */
@@ -410,6 +411,19 @@ uint64_t pick_chunk(uint64_t units, uint64_t slots, uint64_t min_chunk) {
 }
 
 template <int KIND, typename CodeT>
+int launch_stream3(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t smem) {
+    auto kern = tab_smem ? k_stream3<KIND, CodeT, true> : k_stream3<KIND, CodeT, false>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    kern<<<P.streams, S3_THREADS, smem, ctx->stream>>>(P);
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
+
+template <int KIND, typename CodeT>
 int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t smem) {
     auto kern = tab_smem ? k_stream2<KIND, CodeT, true> : k_stream2<KIND, CodeT, false>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -453,6 +467,21 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.traj_hash = od.hash;
     P.sums = od.sums;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
+    if (ctx->stream3) { /* one CTA of three warps per stream (k_stream3) */
+        size_t smem3 = 64 + (size_t)GW_RING * 4 + S3_RAWQ_U4 * 16 + (size_t)(P.qlen + 16) * (code8 ? 1 : 2) + 16;
+        const size_t tab3 = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
+        bool tab_smem3 = false;
+        if (KIND == KIND_TREE && smem3 + tab3 + 16 <= 48 * 1024) { /* keep four CTAs per SM */
+            tab_smem3 = true;
+            smem3 += tab3 + 16;
+        }
+        if (code8)
+            rc = launch_stream3<KIND, uint8_t>(ctx, P, tab_smem3, smem3);
+        else
+            rc = launch_stream3<KIND, uint16_t>(ctx, P, tab_smem3, smem3);
+        if (rc) return rc;
+        return fetch_end_window(ctx);
+    }
     const size_t queue_bytes = (size_t)GW_PAIRS * (P.qlen + 16) * (code8 ? 1 : 2);
     size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + queue_bytes + 16;
     const size_t tab_bytes = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
@@ -881,6 +910,10 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "lane_full_columns")) {
         ctx->lane_full_columns = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "stream3")) {
+        ctx->stream3 = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "small_path")) {

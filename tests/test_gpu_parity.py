@@ -447,3 +447,25 @@ def test_nine_transitions_are_refused(ctx):
     with pytest.raises(PcuError) as e:
         ctx.rollout_random_tree(64, rows=2, cols=2, transitions=9, depth=3, engine=Engine(0), payoff=np.zeros(64, np.uint8))
     assert e.value.code == -3
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[1], CASES[3], CASES[6]])
+def test_stream3_variant_is_bit_exact(ctx, oracle, case):
+    """k_stream3 (option stream3 = 1): the role-split variant of the fused kernel — recurrence, temper and walk in
+    separate warps handing off through mbarriers.  Slower than k_stream2 on B200 (profiles/README.md r1h), kept
+    selectable; it must give the same bytes."""
+    rows, cols, T, thr, depth, sseed, pre, tseed, bias, mseed, mpre = case
+    n = 5000
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth,
+                                      state_seed=sseed, state_pre_discard=pre, transition_seed=tseed, payoff_bias=bias,
+                                      model_seed=mseed, model_pre_discard=mpre)
+    eng = Engine(mseed).discard(mpre)
+    ctx.set_option("stream3", 1)
+    try:
+        got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
+                       bias=bias, engine=eng)
+    finally:
+        ctx.set_option("stream3", 0)
+    assert ctx.last_path == "stream_table"
+    check_same(got, exp, n)
+    assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
