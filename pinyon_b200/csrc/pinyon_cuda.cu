@@ -60,6 +60,7 @@ struct pcu_ctx {
     uint64_t launches = 0;
     int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
     int force_general = 0;
+    int rb = 32;        /* rollouts per consumer batch of the fused kernels (32 or 64) */
     int stream3 = 0;    /* fused path: k_stream3 (five role warps per stream) instead of k_stream2; measured slower (1.20 vs 1.11 ms) */
     int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
     bool small_attr[2] = {false, false};
@@ -443,7 +444,7 @@ constexpr size_t SMEM_LIMIT = 200 * 1024;
  * memory; deeper batches take the general path (codes through HBM). */
 bool stream_fits(uint32_t depth, uint64_t actions) {
     uint64_t qlen = 1024;
-    while (qlen < 2ull * 32 * depth + 2 * GW_PASS_STEPS) qlen <<= 1;
+    while (qlen < 2ull * 64 * depth + 2 * GW_PASS_STEPS) qlen <<= 1;
     const size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + (size_t)GW_PAIRS * (qlen + 16) * (actions <= 256 ? 1 : 2) + 16;
     return smem <= SMEM_LIMIT;
 }
@@ -455,7 +456,7 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     const uint64_t slots = (uint64_t)ctx->sms * ctx->streams_per_sm;
     P.chunk = pick_chunk(n, slots, 128);
     P.streams = (uint32_t)((n + P.chunk - 1) / P.chunk);
-    P.rb = 32;
+    P.rb = ctx->rb;
     P.qlen = 1024;
     while (P.qlen < 2ull * P.rb * P.depth + 2 * GW_PASS_STEPS) P.qlen <<= 1;
     int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, P.streams, 4ull * P.depth * P.chunk);
@@ -910,6 +911,11 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "lane_full_columns")) {
         ctx->lane_full_columns = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "rb")) {
+        if (value != 32 && value != 64) return PCU_ERR_INVALID;
+        ctx->rb = (int)value;
         return PCU_OK;
     }
     if (!strcmp(key, "stream3")) {

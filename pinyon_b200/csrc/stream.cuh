@@ -244,7 +244,7 @@ template <bool TRAJ, typename CodeT>
 __device__ __forceinline__ uint32_t walk_mold(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
                                               uint8_t *tr) {
     uint32_t h = PCU_HASH_INIT;
-#pragma unroll 2
+#pragma unroll 5
     for (uint32_t s = 0; s < d; ++s) {
         const uint32_t code = queue[(qb + s) & qmask];
         h = hash_step(h, code, 0);
@@ -260,7 +260,7 @@ __device__ __forceinline__ uint32_t walk_tree1(const CodeT *queue, uint32_t qmas
                                                const int8_t *tb, uint32_t p, uint32_t adv, int &bias, uint8_t *tr) {
     uint32_t h = PCU_HASH_INIT;
     int b = bias;
-#pragma unroll 2
+#pragma unroll 5
     for (uint32_t s = 0; s < d; ++s) {
         const uint32_t code = queue[(qb + s) & qmask];
         const uint32_t t = p + code; /* discard(row*cols + col): random-tree.hh:88-89 */
@@ -281,7 +281,7 @@ __device__ __forceinline__ uint32_t walk_treeT(const CodeT *queue, uint32_t qmas
     uint32_t h = PCU_HASH_INIT;
     int b = bias;
     uint32_t gb = p - gen_words; /* where the current chance strategies were drawn */
-#pragma unroll 2
+#pragma unroll 5
     for (uint32_t s = 0; s < d; ++s) {
         const uint32_t code = queue[(qb + s) & qmask];
         const uint32_t st = code * T;

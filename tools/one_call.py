@@ -10,6 +10,8 @@ sps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
 n = 1 << (int(sys.argv[3]) if len(sys.argv) > 3 else 24)
 ctx = Context(0)
 ctx.set_option("streams_per_sm", sps)
+import os
+if os.environ.get("PCU_RB"): ctx.set_option("rb", int(os.environ["PCU_RB"]))
 dev = torch.device("cuda", 0)
 payoff = torch.empty(n, dtype=torch.uint8, device=dev)
 sums = torch.zeros(8, dtype=torch.int64, device=dev)
