@@ -44,9 +44,9 @@ WORKLOADS = {
     # config B with distinct roots and distinct transition seeds -> k_seed_pre + k_warp (private
     # 624-word engines refilled ~19.5 times per rollout).  2^20 rollouts per GPU (the CPU needs ~0.3 ms per rollout).
     # ops_setup = 2492 (state seeding) + 1592 (transition prng); ops_exec per rollout = 430 warp instructions per step
-    # x 32 lanes x 20 steps (ncu r1e) is what the kernel issues, most of it the refills.
+    # of which 55 % are int32 ALU/FMA-pipe instructions (ncu r1e, r1g) x 32 lanes = 7150 int ops per step.
     "tree_d20_9x9x3_dr": dict(kind="tree", rows=9, cols=9, T=3, depth=20, log2n=20, ops_step=4920.0, ops_setup=4084.0,
-                              ops_exec=12800.0, dr=True, kernel="k_seed_pre + k_warp<TREE,S>"),
+                              ops_exec=7150.0, dr=True, kernel="k_seed_pre + k_warp<TREE,S>"),
     "mold_2_10": dict(kind="mold", rows=2, cols=2, T=1, depth=10, log2n=24, ops_step=104.0, ops_exec=70.0,
                       kernel="k_stream2<MOLD,u8>"),
 }
