@@ -54,6 +54,14 @@ struct pcu_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr; /* bracket the rollout kernel of the last call */
+    cudaStream_t copy_stream = nullptr;       /* H2D staging of batch inputs, overlapped with the model-stream kernels */
+    cudaEvent_t ev_in = nullptr;
+    struct PendingCopy {
+        void *dst;
+        const void *src;
+        size_t bytes;
+    };
+    std::vector<PendingCopy> pending_in; /* stage_in copies not yet enqueued (see inputs_ready) */
     bool ev_valid = false;
     std::string err;
     std::string path;
@@ -270,8 +278,21 @@ int stage_in(pcu_ctx *ctx, int mem, const T *src, uint64_t n, BufId id, const T 
         return PCU_OK;
     }
     CU(ctx->buf[id].ensure(sizeof(T) * n));
-    CU(cudaMemcpyAsync(ctx->buf[id].p, src, sizeof(T) * n, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->pending_in.push_back({ctx->buf[id].p, src, sizeof(T) * n});
     *dev_out = reinterpret_cast<const T *>(ctx->buf[id].p);
+    return PCU_OK;
+}
+
+/* Enqueue the copies stage_in collected on the copy stream and make the work queued on ctx->stream from here on wait
+ * for them.  Called late on purpose where the first kernels need no batch arrays: H2D copies of all streams drain
+ * through one hardware queue in issue order, so a 134 MB seed array enqueued first would hold back the 2.5 KB engine
+ * window the model-stream kernels start from (measured: no overlap at all). */
+int inputs_ready(pcu_ctx *ctx) {
+    for (const auto &c : ctx->pending_in)
+        CU(cudaMemcpyAsync(c.dst, c.src, c.bytes, cudaMemcpyHostToDevice, ctx->copy_stream));
+    ctx->pending_in.clear();
+    CU(cudaEventRecord(ctx->ev_in, ctx->copy_stream));
+    CU(cudaStreamWaitEvent(ctx->stream, ctx->ev_in, 0));
     return PCU_OK;
 }
 
@@ -858,7 +879,9 @@ int pcu_create(int device_id, pcu_ctx **out) {
         return PCU_ERR_CUDA;
     }
     ctx->stream = ctx->own_stream;
-    if (cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess) {
+    if (cudaEventCreate(&ctx->ev0) != cudaSuccess || cudaEventCreate(&ctx->ev1) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->ev_in, cudaEventDisableTiming) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess) {
         delete ctx;
         return PCU_ERR_CUDA;
     }
@@ -876,6 +899,8 @@ void pcu_destroy(pcu_ctx *ctx) {
     if (ctx->pin_out) cudaFreeHost(ctx->pin_out);
     if (ctx->ev0) cudaEventDestroy(ctx->ev0);
     if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+    if (ctx->ev_in) cudaEventDestroy(ctx->ev_in);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -1050,6 +1075,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     const int32_t *d_bias;
     const uint64_t *d_sseed, *d_tseed, *d_mseed = nullptr;
     const uint16_t *d_depth;
+    ctx->pending_in.clear();
     if ((rc = stage_in(ctx, b->mem, b->state_pos, n, B_STATE_POS, &d_pos))) return rc;
     if ((rc = stage_in(ctx, b->mem, b->payoff_bias, n, B_BIAS, &d_bias))) return rc;
     if ((rc = stage_in(ctx, b->mem, b->state_seed, n, B_STATE_SEED, &d_sseed))) return rc;
@@ -1058,6 +1084,10 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+    /* mode S with uniform depth: the action-code generator needs none of the batch arrays, so the copies above are
+     * enqueued behind it and run beside it on the copy stream */
+    const bool defer_inputs = rng->mode == PCU_MODEL_STREAM && !b->depth && b->mem == PCU_MEM_HOST;
+    if (!defer_inputs && (rc = inputs_ready(ctx))) return rc;
 
     const double *d_fq = nullptr;
     uint32_t fq_w = 0;
@@ -1084,6 +1114,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         if (span > (1u << 22)) fused = false;
     }
     if (fused) {
+        if (defer_inputs && (rc = inputs_ready(ctx))) return rc;
         const uint32_t tab_base = pos_min - gen_words;
         const uint32_t tab_len = (uint32_t)span;
         const double pu = (T > 1) ? host_uniform_from_seed(b->transition_seed_u) : 0.0;
@@ -1157,6 +1188,21 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     W.sums = od.sums;
     /* lane-per-rollout kernel: transitions == 1 (draw positions depend on the action codes only) and every
      * read inside the first refill of the state engine; mode P also needs 4 dmax model words below 227 */
+    if (rng->mode == PCU_MODEL_STREAM) {
+        uint64_t total_steps = n * (uint64_t)b->depth_u;
+        if (d_depth) {
+            if ((rc = scan_depths(ctx, d_depth, n, &W.step_off, &total_steps))) return rc;
+        }
+        bool c16;
+        if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16))) return rc;
+        W.codes = ctx->buf[B_CODES].p;
+        W.code_u16 = c16;
+    } else {
+        W.model_seeds = d_mseed;
+    }
+    if (defer_inputs && (rc = inputs_ready(ctx))) return rc;
+    /* lane-per-rollout kernel: transitions == 1 (draw positions depend on the action codes only) and every
+     * read inside the first refill of the state engine; mode P also needs 4 dmax model words below 227 */
     uint64_t lane_words = 0, lane_dmax = 0;
     LaneGeom geom;
     bool lane = !ctx->force_warp && T == 1;
@@ -1171,29 +1217,13 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         geom.dmax = (uint32_t)lane_dmax;
     }
     if (rng->mode == PCU_MODEL_STREAM) {
-        uint64_t total_steps = n * (uint64_t)b->depth_u;
-        if (d_depth) {
-            if ((rc = scan_depths(ctx, d_depth, n, &W.step_off, &total_steps))) return rc;
-        }
-        bool c16;
-        if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16))) return rc;
-        W.codes = ctx->buf[B_CODES].p;
-        W.code_u16 = c16;
         ctx->path = lane ? "lane_private_S" : "warp_private_S";
-        if (lane)
-            rc = launch_lane<KIND_TREE, 0>(ctx, W, geom);
-        else
-            rc = launch_warp<KIND_TREE, 0>(ctx, W);
-        if (rc) return rc;
+        rc = lane ? launch_lane<KIND_TREE, 0>(ctx, W, geom) : launch_warp<KIND_TREE, 0>(ctx, W);
     } else {
-        W.model_seeds = d_mseed;
         ctx->path = lane ? "lane_private_P" : "warp_private_P";
-        if (lane)
-            rc = launch_lane<KIND_TREE, 1>(ctx, W, geom);
-        else
-            rc = launch_warp<KIND_TREE, 1>(ctx, W);
-        if (rc) return rc;
+        rc = lane ? launch_lane<KIND_TREE, 1>(ctx, W, geom) : launch_warp<KIND_TREE, 1>(ctx, W);
     }
+    if (rc) return rc;
     return finish_all(ctx, out, n, od, rng);
 }
 
@@ -1225,9 +1255,11 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
     if (n == 0) return finish_all(ctx, out, n, od, rng);
     const uint16_t *d_depth;
     const uint64_t *d_mseed = nullptr;
+    ctx->pending_in.clear();
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+    if ((rc = inputs_ready(ctx))) return rc;
 
     if (!ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && b->depth_u > 0 &&
         stream_fits(b->depth_u, (uint64_t)b->n_actions * b->n_actions)) {
