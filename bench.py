@@ -32,8 +32,11 @@ sys.path.insert(0, str(ROOT))
 
 WORKLOADS = {
     # name: (kind, rows, cols, transitions, depth, log2 n per gpu, algorithmic int32 ops/step, ops/rollout setup)
+    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of k_stream2 from the ncu --set full capture of this build
+    # (profiles/r1i_ncu_full_summary.csv, 2^24 rollouts): 1.53 MB read, 0 written — under ncu the 16.8 MB of payoff
+    # bytes were still in L2 when the kernel ended; they reach HBM later (or go straight to the host when zero-copy).
     "tree_d10_3x3x1": dict(kind="tree", rows=3, cols=3, T=1, depth=10, log2n=24, ops_step=318.0, ops_exec=76.0,
-                           kernel="k_stream2<TREE,u8,tab_smem>"),
+                           kernel="k_stream2<TREE,u8,tab_smem>", traffic=1528320.0),
     "tree_d20_9x9x3": dict(kind="tree", rows=9, cols=9, T=3, depth=20, log2n=24, ops_step=4920.0, ops_exec=80.0,
                            kernel="k_stream2<TREE,u8,tab_smem>"),
     # distinct roots (state_seed_i = i): every rollout owns a private state engine, so the
@@ -443,7 +446,8 @@ def run_ours(args, w):
             "roofline": {"bound": "int_issue", "kernel": w["kernel"], "kernel_ms": k_ms,
                          "kernel_share_of_step": k_ms / ms_step,
                          "achieved": achieved / 1e9, "peak": int_peak / 1e9, "unit": "Gop/s",
-                         "frac": achieved / int_peak, "traffic": None,
+                         "frac": achieved / int_peak,
+                         "traffic": w.get("traffic") if n == (1 << 24) else None,
                          "executed": {"ops_per_step": w["ops_exec"], "achieved": executed / 1e9,
                                       "frac": executed / int_peak, "frac_of_alu_pipe": executed / int_peak_alu},
                          "note": note,
