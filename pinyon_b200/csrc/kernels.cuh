@@ -291,12 +291,11 @@ __device__ __forceinline__ void warp_body(const WarpParams &P, const SmallExtra 
         uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
 
         for (uint32_t s = 0; s < d; ++s) {
-            uint32_t r, c;
+            uint32_t r = 0, c = 0, joint;
             if (MODE == 0) {
-                const uint32_t code = P.code_u16 ? (uint32_t)((const uint16_t *)P.codes)[soff + s]
-                                                 : (uint32_t)((const uint8_t *)P.codes)[soff + s];
-                r = code / P.cols;
-                c = code - r * P.cols;
+                /* the joint code is all a step needs; row and column are split off only for a trajectory */
+                joint = P.code_u16 ? (uint32_t)((const uint16_t *)P.codes)[soff + s]
+                                   : (uint32_t)((const uint8_t *)P.codes)[soff + s];
             } else {
                 /* lanes 0..3 draw the four model words of this step (monte-carlo-model.hh:89-90) */
                 const int mrel = (int)(moff + 4ll * s - em.base);
@@ -311,8 +310,8 @@ __device__ __forceinline__ void warp_body(const WarpParams &P, const SmallExtra 
                 const uint32_t vv = mod32(m * mc.c32 + lo, mc.n, mc.m);
                 r = __shfl_sync(PCU_FULL, vv, 0);
                 c = __shfl_sync(PCU_FULL, vv, 2);
+                joint = r * P.cols + c;
             }
-            const uint32_t joint = r * P.cols + c;
             uint32_t ch = 0;
             if (KIND == KIND_TREE) {
                 const uint32_t T = P.T;
@@ -363,6 +362,10 @@ __device__ __forceinline__ void warp_body(const WarpParams &P, const SmallExtra 
             }
             h = hash_step(h, joint, ch);
             if (tr && lane == 0) {
+                if (MODE == 0) {
+                    r = joint / P.cols;
+                    c = joint - r * P.cols;
+                }
                 tr[3 * s + 0] = (uint8_t)r;
                 tr[3 * s + 1] = (uint8_t)c;
                 tr[3 * s + 2] = (uint8_t)ch;
