@@ -164,3 +164,20 @@ def test_golden_file_is_current(reference):
     e = GOLDEN["tree"][1]
     b = loader.random_tree_rollouts(reference, e["n"], prefix="ref", **_case_kwargs(e["case"]))
     assert b["payoff"].tolist() == e["payoff_x2"]
+
+
+def test_nine_transitions_overflow_int_in_the_reference(oracle):
+    """random-tree.hh:165-184 accumulates n_k/10 as Rational<int> (rational.hh:82-87: p = p*10 + n*q, q *= 10) before
+    reducing: at T = 9 the numerator 10^8 * sum(n_k) passes 2^31, so the reference's chance strategies stop being
+    probability vectors (signed overflow: undefined behaviour that wraps here).  T = 8 is the last exact case —
+    SURVEY.md App. C6 put the limit at 9 — and libpinyon_cuda refuses T > 8 (tests/test_gpu_parity.py)."""
+    def cells(T, seed):
+        strat = np.zeros(2 * 2 * T)
+        oracle.orc_random_tree_root_strategies(seed, 0, 5, 2, 2, T, 0, 1, strat.ctypes.data)
+        return strat.reshape(4, T)
+
+    def is_distribution(cell):
+        return abs(cell.sum() - 1) < 1e-12 and (cell >= 0).all() and (cell <= 1).all()
+
+    assert all(is_distribution(c) for seed in range(20) for c in cells(8, seed))
+    assert not any(is_distribution(c) for seed in range(20) for c in cells(9, seed))
