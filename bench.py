@@ -437,7 +437,7 @@ def run_ours(args, w):
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": describe(w, n), "l2": "flushed between steps by a 256 MiB device write",
                        "parallelism": f"dp{world}: rollout-index shards of one model stream, NCCL all-reduce of sums only",
-                       "streams_per_sm": args.streams_per_sm or 4},
+                       "streams_per_sm": args.streams_per_sm or ("auto: 8 from 2.5e8 rollout-steps per call, else 4")},
             "rollout_steps_per_sec": value * depth,
             "e2e": {"value": e2e, "unit": "rollouts/s", "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": n + 64 + 624 * 4, "rollout_steps_per_sec": e2e * depth},

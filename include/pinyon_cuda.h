@@ -61,7 +61,7 @@ uint64_t pcu_kernel_launches(const pcu_ctx *ctx);
 /* Device time in ms of the rollout kernel (k_stream2 / k_warp) of the last rollout call,
  * from CUDA events recorded on the launching stream around that launch; -1 if none. */
 double pcu_last_kernel_ms(pcu_ctx *ctx);
-/* Tuning knobs, mainly for benchmarks: key "streams_per_sm" (1..16, default 4) sets how many
+/* Tuning knobs, mainly for benchmarks: key "streams_per_sm" (1..16; default 0 = 4, or 8 for calls of >= 2.5e8 rollout-steps) sets how many
  * model-stream generator warps the fused kernels keep resident per SM (each needs one
  * jump-ahead checkpoint per call).  Returns PCU_ERR_INVALID for unknown keys. */
 int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value);

@@ -66,7 +66,7 @@ struct pcu_ctx {
     std::string err;
     std::string path;
     uint64_t launches = 0;
-    int streams_per_sm = 4; /* model streams (generator warps) resident per SM */
+    int streams_per_sm = 0; /* model streams (generator warps) resident per SM; 0 = by batch size (run_stream) */
     int force_general = 0;
     int rb = 32;        /* rollouts per consumer batch of the fused kernels (32 or 64) */
     int stream3 = 0;    /* fused path: k_stream3 (five role warps per stream) instead of k_stream2; measured slower (1.20 vs 1.11 ms) */
@@ -474,7 +474,11 @@ bool stream_fits(uint32_t depth, uint64_t actions) {
 template <int KIND>
 int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od) {
     const uint64_t n = P.n;
-    const uint64_t slots = (uint64_t)ctx->sms * ctx->streams_per_sm;
+    /* Every stream costs one jump-ahead checkpoint (~0.5 us of the whole GPU) and a second generator warp per
+     * scheduler hides the first one's fixed-latency stalls: worth it from ~2.5e8 rollout-steps per call on
+     * (tools/sweep_stream.py: config B 2.78 -> 2.52 ms at 8 per SM, config A 1.41 -> 1.53 ms). */
+    const int per_sm = ctx->streams_per_sm ? ctx->streams_per_sm : ((double)n * P.depth >= 2.5e8 ? 8 : 4);
+    const uint64_t slots = (uint64_t)ctx->sms * per_sm;
     P.chunk = pick_chunk(n, slots, 128);
     P.streams = (uint32_t)((n + P.chunk - 1) / P.chunk);
     P.rb = ctx->rb;
@@ -525,7 +529,7 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
 int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, pcu_model_rng *rng, bool *code16) {
     const bool c16 = (uint64_t)rows * cols > 256;
     *code16 = c16;
-    const uint64_t slots = (uint64_t)ctx->sms * ctx->streams_per_sm;
+    const uint64_t slots = (uint64_t)ctx->sms * (ctx->streams_per_sm ? ctx->streams_per_sm : 4);
     const uint64_t chunk = pick_chunk(total_steps ? total_steps : 1, slots, 4096); /* steps per stream */
     uint64_t streams = (total_steps + chunk - 1) / chunk;
     if (streams == 0) streams = 1;
@@ -926,7 +930,7 @@ int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream) {
 int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     if (!ctx || !key) return PCU_ERR_INVALID;
     if (!strcmp(key, "streams_per_sm") || !strcmp(key, "ctas_per_sm")) { /* second name: r1a spelling */
-        if (value < 1 || value > 16) return fail(ctx, PCU_ERR_INVALID, "streams_per_sm must be 1..16");
+        if (value < 0 || value > 16) return fail(ctx, PCU_ERR_INVALID, "streams_per_sm must be 0 (auto) or 1..16");
         ctx->streams_per_sm = (int)value;
         return PCU_OK;
     }
