@@ -112,7 +112,10 @@ int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint6
  *                    2*rows*cols*transitions of its latest get_chance_strategies()
  *                    (ctor :31-41 or apply_actions :105-107)
  *   transition_seed  (:15,59-61)
- *   depth            depth_bound (:16), >= 1
+ *   depth            depth_bound (:16), >= 1.  A zero ENTRY of a per-rollout depth array plays no step and
+ *                    returns the payoff of its payoff_bias (the drop-in model never sends such states: terminal
+ *                    states are answered on the host); a batch-uniform depth of 0 is refused, because the
+ *                    reference never terminates from a depth_bound == 0 root (:95-99)
  *   payoff_bias      (:20)
  *   rows, cols, transitions, chance_threshold = thr_p/thr_q  (:17-21) batch-uniform
  * Only the default growth functions (:141-146) are reproduced. */
