@@ -356,7 +356,12 @@ def run_ours(args, w):
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
-    time.sleep(0.25)
+    # nvidia-smi takes up to a second to attach to the driver, and launches stall while it does: wait for its first
+    # sample so that only steady 100 ms polling overlaps the timed region (a 1.66 ms outlier step was seen otherwise)
+    t_wait = time.time()
+    while not sampler.rows and time.time() - t_wait < 3.0:
+        time.sleep(0.05)
+    time.sleep(0.1)
     launches0 = ctx.launches
     starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
