@@ -55,6 +55,32 @@ static_assert(JA_ACTIVE * JA_OUT >= MT_N && JA_ACTIVE <= JA_SEG_THREADS, "output
 static_assert(JA_EXT_WORDS >= 32 * (MT_N - 1) + JA_OUT * (JA_ACTIVE - 1) + 32 + JA_OUT - 1, "extension too short for the last lane");
 constexpr size_t JA_SMEM = sizeof(uint32_t) * (JA_EXT_WORDS + MTJ_POLY_WORDS + JA_SEGS * MT_N);
 
+/* acc[m] ^= XOR of r[m + b] over the set bits b of the 4-bit pattern P: terms are folded two at a time
+ * into three-input LOP3s (1, 1, 2, 2 instructions per output for 1..4 set bits; 1.25 per nibble on average
+ * against 1.5 for two pairs), and one branch serves four coefficients instead of two. */
+template <unsigned P>
+__device__ __forceinline__ void ja_nibble(uint32_t (&acc)[JA_OUT], const uint32_t *r) {
+    constexpr int b0 = (P & 1u) ? 0 : (P & 2u) ? 1 : (P & 4u) ? 2 : 3;
+    constexpr unsigned P1 = P & (P - 1u);
+    constexpr int b1 = (P1 & 2u) ? 1 : (P1 & 4u) ? 2 : 3;
+    constexpr unsigned P2 = P1 & (P1 - 1u);
+    constexpr int b2 = (P2 & 4u) ? 2 : 3;
+    constexpr unsigned P3 = P2 & (P2 - 1u);
+#pragma unroll
+    for (int m = 0; m < JA_OUT; ++m) {
+        if (P1 == 0)
+            acc[m] ^= r[m + b0];
+        else
+            acc[m] ^= r[m + b0] ^ r[m + b1];
+        if (P2 != 0) {
+            if (P3 == 0)
+                acc[m] ^= r[m + b2];
+            else
+                acc[m] ^= r[m + b2] ^ r[m + 3];
+        }
+    }
+}
+
 __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
     k_jump_apply(const uint32_t *__restrict__ ext, const uint32_t *__restrict__ polys, uint32_t splits, uint32_t *d_ck) {
     extern __shared__ __align__(16) uint32_t ja_smem[];
@@ -90,18 +116,29 @@ __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
 #pragma unroll
             for (int k = 0; k < 32 + JA_OUT - 1; ++k) r[k] = p[k];
 #pragma unroll
-            for (int k = 0; k < 32; k += 2) { /* two coefficients at a time: both set is ONE three-input LOP3 per output */
-                const uint32_t two = (pw >> k) & 3u;
-                if (two == 3u) {
-#pragma unroll
-                    for (int m = 0; m < JA_OUT; ++m) acc[m] ^= r[k + m] ^ r[k + 1 + m];
-                } else if (two == 1u) {
-#pragma unroll
-                    for (int m = 0; m < JA_OUT; ++m) acc[m] ^= r[k + m];
-                } else if (two == 2u) {
-#pragma unroll
-                    for (int m = 0; m < JA_OUT; ++m) acc[m] ^= r[k + 1 + m];
+            for (int k = 0; k < 32; k += 4) { /* four coefficients at a time behind one warp-uniform 16-way branch */
+                /* an explicit tree of single-bit tests on pw: one LOP3-to-predicate per level, no field extraction */
+#define JA_B(b) (pw & ((1u << (b)) << k))
+#define JA_L(P) ja_nibble<P>(acc, r + k)
+                if (JA_B(3)) {
+                    if (JA_B(2)) {
+                        if (JA_B(1)) { if (JA_B(0)) JA_L(15); else JA_L(14); }
+                        else { if (JA_B(0)) JA_L(13); else JA_L(12); }
+                    } else {
+                        if (JA_B(1)) { if (JA_B(0)) JA_L(11); else JA_L(10); }
+                        else { if (JA_B(0)) JA_L(9); else JA_L(8); }
+                    }
+                } else {
+                    if (JA_B(2)) {
+                        if (JA_B(1)) { if (JA_B(0)) JA_L(7); else JA_L(6); }
+                        else { if (JA_B(0)) JA_L(5); else JA_L(4); }
+                    } else {
+                        if (JA_B(1)) { if (JA_B(0)) JA_L(3); else JA_L(2); }
+                        else { if (JA_B(0)) JA_L(1); }
+                    }
                 }
+#undef JA_B
+#undef JA_L
             }
         }
 #pragma unroll
