@@ -1,5 +1,5 @@
 """Randomised differential test: libpinyon_cuda against the oracle over random shapes, batch kinds and paths.
-python tools/fuzz_parity.py [cases] [seed]   (GPU box; prints the path histogram, exits 1 on the first mismatch)"""
+python tests/fuzz_parity.py [cases] [seed]   (GPU box; prints the path histogram, exits 1 on the first mismatch)"""
 import collections, sys
 from pathlib import Path
 sys.path.insert(0, str(Path(__file__).resolve().parent.parent))

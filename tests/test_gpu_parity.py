@@ -473,13 +473,13 @@ def test_stream3_variant_is_bit_exact(ctx, oracle, case):
 
 @pytest.mark.parametrize("args", [("80", "7"), ("80", "8", "lane")])
 def test_randomised_differential(args):
-    """tools/fuzz_parity.py: random shapes, batch kinds and model modes against the oracle, every kernel path."""
+    """tests/fuzz_parity.py: random shapes, batch kinds and model modes against the oracle, every kernel path."""
     import subprocess
     import sys
     from pathlib import Path
 
     root = Path(__file__).resolve().parent.parent
-    res = subprocess.run([sys.executable, str(root / "tools" / "fuzz_parity.py"), *args], capture_output=True, text=True,
+    res = subprocess.run([sys.executable, str(root / "tests" / "fuzz_parity.py"), *args], capture_output=True, text=True,
                          timeout=900)
     assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
     assert "bit-exact" in res.stdout
