@@ -420,14 +420,15 @@ int fetch_end_window(pcu_ctx *ctx) {
 }
 
 /* Work per model stream (one generator warp).  Every distinct stride needs its own family of
- * jump polynomials (cached, ~80 ms to build), so chunk sizes are quantised to four significant
- * bits: at most 1/16 of the stream slots idle, a bounded set of strides per depth. */
+ * jump polynomials (cached, ~80 ms to build), so chunk sizes are quantised to seven significant
+ * bits: at most 1/64 of a stream's work is padding (1/16 with five bits cost config A 1.2 %), and the set of
+ * strides per depth stays bounded. */
 uint64_t pick_chunk(uint64_t units, uint64_t slots, uint64_t min_chunk) {
     uint64_t c = (units + slots - 1) / slots;
     if (c < min_chunk) c = min_chunk;
-    if (c < 32) return c;
+    if (c < 128) return c;
     int e = 0;
-    while ((c >> e) >= 32) ++e; /* c >> e in [16, 32) */
+    while ((c >> e) >= 128) ++e; /* c >> e in [64, 128) */
     const uint64_t m = (c + (1ull << e) - 1) >> e;
     return m << e;
 }
