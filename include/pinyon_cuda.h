@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define PCU_VERSION 100
+#define PCU_VERSION 200
 
 #define PCU_OK 0
 #define PCU_ERR_INVALID (-1)     /* bad argument (null pointer, depth 0, rows or cols > 255, ...) */
@@ -50,6 +50,19 @@ typedef struct pcu_ctx pcu_ctx;
 /* Create a context on CUDA device `device_id`.  Fails with PCU_ERR_CUDA if there is
  * no such device or it is not compute capability 10.x. */
 int pcu_create(int device_id, pcu_ctx **out);
+/* Create ONE context over `n` GPUs of this box (north_star (d), SURVEY.md 8(e): one process, ncclCommInitAll).
+ * A rollout call on it is cut into contiguous rollout-index shards, one per GPU, each played by that GPU's own
+ * streams from its slice of the ONE model stream (the shard's jump-ahead polynomials are applied on the GPU to
+ * the caller's engine: no host-side jump), the outputs land in the caller's arrays at the shard's offset, and the
+ * eight u64 counters of pcu_out.sums are summed over the GPUs with one ncclAllReduce(ncclUint64, ncclSum) — the
+ * path's only collective.  Results, including the post-batch engine, are byte-identical to the same call on one GPU.
+ * Batches must live in HOST memory (pinned, from pcu_host_alloc, for zero-copy stores from every GPU); batches
+ * below 65 536 rollouts per GPU (option "multi_min_rollouts") and device-memory batches run on device_ids[0] alone.
+ * NCCL is loaded at run time (libnccl.so.2); PCU_ERR_UNSUPPORTED if it is absent and n > 1.  Listing one GPU n
+ * times is allowed (a test configuration: the shards then share the GPU and the counters are summed by a kernel). */
+int pcu_create_multi(const int *device_ids, int n, pcu_ctx **out);
+/* GPUs behind a context: 1 for pcu_create. */
+int pcu_device_count(const pcu_ctx *ctx);
 void pcu_destroy(pcu_ctx *ctx);
 const char *pcu_last_error(const pcu_ctx *ctx);
 int pcu_version(void);
@@ -61,6 +74,14 @@ uint64_t pcu_kernel_launches(const pcu_ctx *ctx);
 /* Device time in ms of the rollout kernel (k_stream2 / k_warp) of the last rollout call,
  * from CUDA events recorded on the launching stream around that launch; -1 if none. */
 double pcu_last_kernel_ms(pcu_ctx *ctx);
+/* Statistics of the last rollout call, for tests and benchmarks: "last_chunk" (rollouts, or steps for ragged batches,
+ * per model stream), "last_streams", "last_family_build_ms" and "last_table_build_ms" (host time the call spent
+ * building a jump-polynomial family / the state-stream table: 0 when cached), "nccl_calls". */
+int pcu_get_stat(pcu_ctx *ctx, const char *key, double *value);
+/* Pay the first-call costs of a batch shape now: builds and uploads the jump-polynomial family that `n`
+ * uniform-depth mode-S rollouts need (~80 ms of host GF(2) arithmetic per new stride; cached afterwards: the
+ * host keeps families up to 256 MiB, option "jump_host_cache_mb", each context `jump_families` = 8 on its GPU). */
+int pcu_warmup(pcu_ctx *ctx, uint64_t n, uint32_t depth);
 /* Tuning knobs, mainly for benchmarks: key "streams_per_sm" (1..16; default 0 = 4, or 8 for calls of >= 2.5e8 rollout-steps) sets how many
  * model-stream generator warps the fused kernels keep resident per SM (each needs one
  * jump-ahead checkpoint per call).  Returns PCU_ERR_INVALID for unknown keys. */
@@ -149,6 +170,8 @@ typedef struct {
  * Replaces ModelOutput::value / ModelBatchOutput (monte-carlo-model.hh:6-32).
  *   payoff_x2[i]  2 * row payoff: 0, 1 (= 1/2) or 2 (RandomTree :99-103); MoldState's
  *                 payoff is never written by the reference, so it is 0 = (0,0).
+ *   payoff_packed2  optional; the same values at 2 bits per rollout, rollout i in bits 2 (i % 4) .. of byte
+ *                 i / 4, (n + 3) / 4 bytes: a quarter of the bytes that cross PCIe per batch
  *   traj          optional; 3 bytes per step (row action, col action, chance action),
  *                 traj_stride steps reserved per rollout, zero filled past the end
  *   traj_hash[i]  optional; FNV-1a style fold of the trajectory:
@@ -164,6 +187,7 @@ typedef struct {
     uint32_t traj_stride;
     uint32_t *traj_hash;
     uint64_t *sums;
+    uint8_t *payoff_packed2;
 } pcu_out;
 
 /* ---- the hot path ------------------------------------------------------------------

@@ -63,6 +63,8 @@ def load_oracle() -> C.CDLL:
     lib.orc_prng_random_int.argtypes = [u64, u64, C.c_int, u64, vp]
     lib.orc_mt_words.argtypes = [u64, u64, u64, vp]
     lib.orc_mt_state.argtypes = [u64, u64, vp, vp]
+    lib.orc_set_model_engine.argtypes = [vp, u32]
+    lib.orc_set_model_engine.restype = None
     lib.orc_random_tree_root_strategies.argtypes = [u64, u64, u32, u32, u32, u32, C.c_int, C.c_int, vp]
     return lib
 
@@ -93,6 +95,12 @@ def load_reference():
             lib._pinyon_path = str(path)
             return lib
     return None
+
+
+def set_model_engine(lib, engine):
+    """The NEXT orc_* rollout call starts its model engine from `engine` (a pinyon_b200.Engine image, e.g.
+    Engine(0).discard(k)) instead of stepping model_pre_discard draws: full-size windows far into the stream."""
+    lib.orc_set_model_engine(engine.x.ctypes.data, int(engine.p[0]))
 
 
 def _arr(a, dtype):

@@ -7,6 +7,7 @@ path here: if the library is missing or no sm_100 device is present, calls raise
 from __future__ import annotations
 
 import ctypes as C
+import weakref
 from pathlib import Path
 from typing import Optional
 
@@ -27,11 +28,18 @@ PCU_MODEL_PER_ROLLOUT = 1
 HASH_INIT = 2166136261
 HASH_MUL = 16777619
 
+
+def unpack2(packed: np.ndarray, n: int) -> np.ndarray:
+    """pcu_out.payoff_packed2 -> one payoff_x2 byte per rollout."""
+    sh = np.arange(4, dtype=np.uint8) * 2
+    return ((packed[:, None] >> sh[None, :]) & 3).astype(np.uint8).reshape(-1)[:n]
+
 # every symbol include/pinyon_cuda.h declares
 EXPORTS = [
     "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches", "pcu_last_kernel_ms",
     "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next", "pcu_mt_discard_family",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
+    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup",
 ]
 
 
@@ -59,7 +67,7 @@ class MoldBatch(C.Structure):
 
 class Out(C.Structure):
     _fields_ = [("mem", C.c_int32), ("payoff_x2", C.c_void_p), ("traj", C.c_void_p), ("traj_stride", C.c_uint32),
-                ("traj_hash", C.c_void_p), ("sums", C.c_void_p)]
+                ("traj_hash", C.c_void_p), ("sums", C.c_void_p), ("payoff_packed2", C.c_void_p)]
 
 
 _lib = None
@@ -110,6 +118,11 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_rollout_random_tree.argtypes = [vp, C.POINTER(RtBatch), C.POINTER(ModelRng), C.POINTER(Out)]
     lib.pcu_rollout_mold.argtypes = [vp, C.POINTER(MoldBatch), C.POINTER(ModelRng), C.POINTER(Out)]
     lib.pcu_measure_int_peak.argtypes = [vp, C.c_int, C.c_int, C.POINTER(C.c_double)]
+    lib.pcu_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
+    lib.pcu_create_multi.restype = C.c_int
+    lib.pcu_device_count.argtypes = [vp]
+    lib.pcu_get_stat.argtypes = [vp, C.c_char_p, C.POINTER(C.c_double)]
+    lib.pcu_warmup.argtypes = [vp, u64, u32]
     _lib = lib
     return lib
 
@@ -165,18 +178,37 @@ def _is_device(*arrays) -> bool:
 class Context:
     """One libpinyon_cuda context (one GPU)."""
 
-    def __init__(self, device: int = 0):
+    def __init__(self, device=0):
+        """device: one CUDA device index (pcu_create) or a sequence of them (pcu_create_multi: one context over
+        several GPUs, batches sharded by rollout index inside the library)."""
         self.lib = load_library()
         h = C.c_void_p()
-        rc = self.lib.pcu_create(device, C.byref(h))
+        if isinstance(device, (list, tuple)):
+            ids = (C.c_int * len(device))(*device)
+            rc = self.lib.pcu_create_multi(ids, len(device), C.byref(h))
+        else:
+            rc = self.lib.pcu_create(device, C.byref(h))
         if rc != PCU_OK:
             raise PcuError(rc, f"pcu_create(device={device}) failed: no sm_100 GPU? (there is no CPU fallback)")
         self.h = h
+        self._pinned = []
 
     def close(self):
         if getattr(self, "h", None):
             self.lib.pcu_destroy(self.h)
             self.h = None
+
+    @property
+    def device_count(self) -> int:
+        return self.lib.pcu_device_count(self.h)
+
+    def stat(self, key: str) -> float:
+        v = C.c_double()
+        self._check(self.lib.pcu_get_stat(self.h, key.encode(), C.byref(v)))
+        return v.value
+
+    def warmup(self, n: int, depth: int):
+        self._check(self.lib.pcu_warmup(self.h, n, depth))
 
     def __del__(self):
         try:
@@ -222,6 +254,8 @@ class Context:
         buf = (C.c_uint8 * nbytes).from_address(p)
         arr = np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)
         arr.flags.writeable = True
+        # cudaFreeHost once the last view of the buffer is gone (the ctypes object is the base of every view)
+        weakref.finalize(buf, self.lib.pcu_host_free, None, p)
         return arr
 
     # -- the hot path ---------------------------------------------------------------
@@ -239,8 +273,9 @@ class Context:
         return r
 
     @staticmethod
-    def _out(device: bool, payoff, traj, traj_stride, traj_hash, sums):
+    def _out(device: bool, payoff, traj, traj_stride, traj_hash, sums, packed=None):
         o = Out()
+        o.payoff_packed2 = _ptr(packed)
         o.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
         o.payoff_x2 = _ptr(payoff)
         o.traj = _ptr(traj)
@@ -251,7 +286,8 @@ class Context:
 
     def rollout_random_tree(self, n, *, rows, cols, transitions=1, thr=(0, 1), depth=None, state_seed=0,
                             state_pos=None, transition_seed=0, payoff_bias=0, engine: Engine = None,
-                            model_seeds=None, payoff=None, traj=None, traj_stride=0, traj_hash=None, sums=None):
+                            model_seeds=None, payoff=None, traj=None, traj_stride=0, traj_hash=None, sums=None,
+                            payoff_packed=None):
         """pcu_rollout_random_tree.  Scalar arguments are batch-uniform; numpy arrays
         (host) or torch CUDA tensors (device) are per-rollout.  state_pos defaults to a
         freshly constructed root: 2*rows*cols*transitions draws."""
@@ -278,14 +314,14 @@ class Context:
         put("payoff_bias", payoff_bias, np.int32)
         b.rows, b.cols, b.transitions = rows, cols, transitions
         b.thr_p, b.thr_q = thr
-        device = _is_device(*arrays, model_seeds, payoff, traj, traj_hash, sums)
+        device = _is_device(*arrays, model_seeds, payoff, traj, traj_hash, sums, payoff_packed)
         b.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
         r = self._rng(engine, model_seeds)
-        o = self._out(device, payoff, traj, traj_stride, traj_hash, sums)
+        o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_random_tree(self.h, C.byref(b), C.byref(r), C.byref(o)))
 
     def rollout_mold(self, n, *, n_actions, depth, engine: Engine = None, model_seeds=None, payoff=None, traj=None,
-                     traj_stride=0, traj_hash=None, sums=None):
+                     traj_stride=0, traj_hash=None, sums=None, payoff_packed=None):
         b = MoldBatch()
         b.n = n
         arrays = []
@@ -296,8 +332,8 @@ class Context:
             arrays.append(depth)
             b.depth = _ptr(depth)
         b.n_actions = n_actions
-        device = _is_device(*arrays, model_seeds, payoff, traj, traj_hash, sums)
+        device = _is_device(*arrays, model_seeds, payoff, traj, traj_hash, sums, payoff_packed)
         b.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
         r = self._rng(engine, model_seeds)
-        o = self._out(device, payoff, traj, traj_stride, traj_hash, sums)
+        o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_mold(self.h, C.byref(b), C.byref(r), C.byref(o)))

@@ -361,7 +361,7 @@ __device__ __forceinline__ void warp_body(const WarpParams &P, const SmallExtra 
                 cur += 2;
             }
             h = hash_step(h, joint, ch);
-            if (tr && lane == 0) {
+            if (tr && lane == 0 && s < P.traj_stride) { /* later steps are played and hashed, not recorded */
                 if (MODE == 0) {
                     r = joint / P.cols;
                     c = joint - r * P.cols;

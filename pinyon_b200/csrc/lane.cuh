@@ -156,7 +156,7 @@ __global__ void __launch_bounds__(32) k_lane(const LaneParams LP) {
                 pos += 2;
             }
             h = hash_step(h, joint, 0);
-            if (tr) {
+            if (tr && s < P.traj_stride) { /* later steps are played and hashed, not recorded */
                 const uint32_t r = joint / P.cols;
                 tr[3 * s + 0] = (uint8_t)r;
                 tr[3 * s + 1] = (uint8_t)(joint - r * P.cols);

@@ -4,6 +4,7 @@
 #include "mt_jump.h"
 
 #include <algorithm>
+#include <chrono>
 #include <cstring>
 
 #include "kernels.cuh"
@@ -11,13 +12,14 @@
 /* ------------------------------------------------------------------ device side */
 
 /* Extend the base window into MTJ_EXT_LEN raw words of its sequence (one CTA). */
-__global__ void __launch_bounds__(GEN_THREADS) k_jump_extend(const uint32_t *ck, uint32_t *ext) {
+__global__ void __launch_bounds__(GEN_THREADS) k_jump_extend(const uint32_t *base, uint32_t *ext, uint32_t *ck0) {
     __shared__ uint32_t ring[RING_WORDS];
     const int t = threadIdx.x;
     for (int i = t; i < MT_N; i += GEN_THREADS) {
-        const uint32_t v = ck[i];
+        const uint32_t v = base[i];
         ring[48 + i] = v;
         ext[i] = v;
+        if (ck0) ck0[i] = v; /* checkpoint 0 of an unsharded batch is the base window itself */
     }
     const ModConst one = {1u, 0xffffffffu, 0u};
     const GenAddr g = make_gen_addr(t, one, one);
@@ -82,12 +84,13 @@ __device__ __forceinline__ void ja_nibble(uint32_t (&acc)[JA_OUT], const uint32_
 }
 
 __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
-    k_jump_apply(const uint32_t *__restrict__ ext, const uint32_t *__restrict__ polys, uint32_t splits, uint32_t *d_ck) {
+    k_jump_apply(const uint32_t *__restrict__ ext, const uint32_t *__restrict__ polys, uint32_t splits, uint32_t *d_ck,
+                 uint32_t skip) {
     extern __shared__ __align__(16) uint32_t ja_smem[];
     uint32_t *sext = ja_smem;
     uint32_t *spoly = ja_smem + JA_EXT_WORDS;
     uint32_t *sred = spoly + MTJ_POLY_WORDS;
-    const uint32_t c = blockIdx.x / splits + 1, sp = blockIdx.x % splits;
+    const uint32_t c = blockIdx.x / splits + skip, sp = blockIdx.x % splits; /* bitmap c of the family -> window c */
     const int tid = threadIdx.x;
     const uint32_t cta_lo = MTJ_POLY_WORDS * sp / splits, cta_hi = MTJ_POLY_WORDS * (sp + 1) / splits;
     {
@@ -157,8 +160,6 @@ __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
     }
 }
 
-int MtJump::run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t count, uint64_t stride, uint32_t *d_ck,
-                uint64_t *launches, std::string *err) {
 #define JCU(call)                                                     \
     do {                                                              \
         cudaError_t e__ = (call);                                     \
@@ -167,34 +168,37 @@ int MtJump::run(cudaStream_t stream, int sms, const uint32_t *base_window, uint6
             return -1;                                                \
         }                                                             \
     } while (0)
-    JCU(cudaMemcpyAsync(d_ck, base_window, sizeof(uint32_t) * MT_N, cudaMemcpyHostToDevice, stream));
-    if (count <= 1) return 0;
+
+/* The device copy of the polynomial family (stride; c = first .. first + count - 1), built and uploaded on a miss. */
+static int family_on_device(MtJump &J, cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride,
+                            MtJump::DevFamily **out, std::string *err) {
+    J.last_build_ms = 0;
     if (!mt_jump_ready()) {
         if (err) *err = "characteristic polynomial computation failed";
         return -1;
     }
-    /* polynomial family of this stride on the device */
-    DevFamily *fam = nullptr;
-    for (auto &f : families)
-        if (f.stride == stride) fam = &f;
+    MtJump::DevFamily *fam = nullptr;
+    for (auto &f : J.families)
+        if (f.stride == stride && f.first == first) fam = &f;
     if (!fam || fam->count < count) {
+        const auto t0 = std::chrono::steady_clock::now();
         std::vector<uint32_t> bits;
         const uint64_t want = std::max<uint64_t>(count, fam ? fam->count : 0);
-        if (!mt_jump_polys(stride, want, bits)) {
+        if (!mt_jump_polys(stride, first, want, bits)) {
             if (err) *err = "jump polynomial computation failed";
             return -1;
         }
         if (!fam) {
-            if (families.size() >= 8) { /* evict the least recently used family */
+            while (J.families.size() >= std::max<size_t>(1, J.max_families)) { /* evict the least recently used family */
                 size_t lru = 0;
-                for (size_t i = 1; i < families.size(); ++i)
-                    if (families[i].last_use < families[lru].last_use) lru = i;
+                for (size_t i = 1; i < J.families.size(); ++i)
+                    if (J.families[i].last_use < J.families[lru].last_use) lru = i;
                 JCU(cudaStreamSynchronize(stream));
-                cudaFree(families[lru].bits);
-                families.erase(families.begin() + lru);
+                cudaFree(J.families[lru].bits);
+                J.families.erase(J.families.begin() + lru);
             }
-            families.push_back(DevFamily{stride, 0, nullptr, 0});
-            fam = &families.back();
+            J.families.push_back(MtJump::DevFamily{stride, first, 0, nullptr, 0});
+            fam = &J.families.back();
         } else {
             JCU(cudaStreamSynchronize(stream));
             cudaFree(fam->bits);
@@ -204,24 +208,48 @@ int MtJump::run(cudaStream_t stream, int sms, const uint32_t *base_window, uint6
         JCU(cudaMalloc(&fam->bits, sizeof(uint32_t) * bits.size()));
         JCU(cudaMemcpy(fam->bits, bits.data(), sizeof(uint32_t) * bits.size(), cudaMemcpyHostToDevice));
         fam->count = want;
+        J.last_build_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     }
-    fam->last_use = ++tick;
+    fam->last_use = ++J.tick;
+    *out = fam;
+    return 0;
+}
+
+int MtJump::prepare(cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride, std::string *err) {
+    if (first == 0 && count <= 1) return 0;
+    DevFamily *fam = nullptr;
+    return family_on_device(*this, stream, first, count, stride, &fam, err);
+}
+
+int MtJump::run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t first, uint64_t count, uint64_t stride,
+                uint32_t *d_ck, uint64_t *launches, std::string *err) {
+    if (first == 0 && count <= 1) {
+        JCU(cudaMemcpyAsync(d_ck, base_window, sizeof(uint32_t) * MT_N, cudaMemcpyHostToDevice, stream));
+        last_build_ms = 0;
+        return 0;
+    }
+    DevFamily *fam = nullptr;
+    if (family_on_device(*this, stream, first, count, stride, &fam, err)) return -1;
     if (!d_ext) {
-        JCU(cudaMalloc(&d_ext, sizeof(uint32_t) * MTJ_EXT_LEN));
+        JCU(cudaMalloc(&d_ext, sizeof(uint32_t) * (MTJ_EXT_LEN + MT_N)));
         JCU(cudaFuncSetAttribute(k_jump_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JA_SMEM));
     }
+    uint32_t *d_base = d_ext + MTJ_EXT_LEN;
+    JCU(cudaMemcpyAsync(d_base, base_window, sizeof(uint32_t) * MT_N, cudaMemcpyHostToDevice, stream));
+    const uint32_t skip = first == 0 ? 1u : 0u; /* window 0 of an unsharded batch needs no polynomial */
+    const uint64_t apply = count - skip;
     /* few checkpoints: split each polynomial over several CTAs so the launch still fills the GPU */
-    uint64_t splits = (2ull * sms + (count - 1) - 1) / (count - 1);
+    uint64_t splits = (2ull * sms + apply - 1) / apply;
     splits = std::max<uint64_t>(1, std::min<uint64_t>(splits, 13));
-    if (splits > 1) JCU(cudaMemsetAsync(d_ck + MT_N, 0, sizeof(uint32_t) * MT_N * (count - 1), stream));
-    k_jump_extend<<<1, GEN_THREADS, 0, stream>>>(d_ck, d_ext);
-    k_jump_apply<<<(unsigned)((count - 1) * splits), JA_SEGS * JA_SEG_THREADS, JA_SMEM, stream>>>(d_ext, fam->bits,
-                                                                                                (uint32_t)splits, d_ck);
+    if (splits > 1) JCU(cudaMemsetAsync(d_ck + (size_t)MT_N * skip, 0, sizeof(uint32_t) * MT_N * apply, stream));
+    k_jump_extend<<<1, GEN_THREADS, 0, stream>>>(d_base, d_ext, skip ? d_ck : nullptr);
+    k_jump_apply<<<(unsigned)(apply * splits), JA_SEGS * JA_SEG_THREADS, JA_SMEM, stream>>>(d_ext, fam->bits, (uint32_t)splits,
+                                                                                         d_ck, skip);
     if (launches) *launches += 2;
     JCU(cudaGetLastError());
     return 0;
-#undef JCU
 }
+#undef JCU
 
 void MtJump::release() {
     for (auto &f : families)

@@ -33,25 +33,35 @@ bool mt_jump_host(uint32_t *window, uint64_t n);
 bool mt_jump_host_family(uint32_t *window, uint64_t stride, uint64_t c);
 
 /* Bitmaps (MTJ_POLY_WORDS u32 each, bit i = coefficient of x^i) of x^(c * stride) mod phi
- * for c = 0..count-1; computed once per stride and cached process-wide. */
-bool mt_jump_polys(uint64_t stride, uint64_t count, std::vector<uint32_t> &bitmaps);
+ * for c = first..first+count-1; computed once per stride and cached process-wide (least recently
+ * used families are dropped once the cache exceeds its byte cap, 256 MiB by default). */
+bool mt_jump_polys(uint64_t stride, uint64_t first, uint64_t count, std::vector<uint32_t> &bitmaps);
+void mt_jump_set_host_cache_bytes(size_t bytes);
 
 struct MtJump {
     /* device copies of polynomial families, keyed by stride */
     struct DevFamily {
         uint64_t stride;
+        uint64_t first; /* bitmaps of c = first .. first + count - 1 */
         uint64_t count;
         uint32_t *bits;
         uint64_t last_use;
     };
     std::vector<DevFamily> families;
+    size_t max_families = 8; /* device copies kept per context (option "jump_families"); evicting one costs a
+                              * stream synchronisation now and a 1.5 MB upload when its stride comes back */
     uint64_t tick = 0;
-    uint32_t *d_ext = nullptr;
+    uint32_t *d_ext = nullptr; /* MTJ_EXT_LEN extended sequence, then the 624-word base window */
+    double last_build_ms = 0;  /* host time spent building/uploading a family in the last run (0: cache hit) */
 
-    /* Fill d_ck[c] (c = 0..count-1) with the window preceding draw c * stride, d_ck[0]
-     * being `base_window` itself.  base_window must stay valid until the stream has consumed
-     * it (pinned staging memory).  Asynchronous on `stream` unless a family has to be built. */
-    int run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t count, uint64_t stride, uint32_t *d_ck,
-            uint64_t *launches, std::string *err);
+    /* Fill d_ck[j] (j = 0..count-1) with the window preceding draw (first + j) * stride counted from
+     * `base_window` (for first == 0, d_ck[0] is base_window itself).  `first` > 0 is how one GPU of a
+     * sharded batch takes its slice of the global checkpoint family without any host-side jump.
+     * base_window must stay valid until the stream has consumed it (pinned staging memory).
+     * Asynchronous on `stream` unless a family has to be built. */
+    int run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t first, uint64_t count, uint64_t stride,
+            uint32_t *d_ck, uint64_t *launches, std::string *err);
+    /* Build and upload the family now (pcu_warmup): the ~80 ms of GF(2) arithmetic a new stride costs. */
+    int prepare(cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride, std::string *err);
     void release();
 };

@@ -238,9 +238,28 @@ Bits pow_x(uint64_t n) {
 /* Per stride: x^(c * stride) mod phi for c = 0, 1, 2, ..., grown on demand. */
 struct Family {
     std::vector<Bits> g;
+    uint64_t last_use = 0;
 };
 std::mutex g_mu;
 std::map<uint64_t, Family> g_families;
+uint64_t g_tick = 0;
+size_t g_family_cap_bytes = size_t(256) << 20; /* host cache of polynomial families; least recently used go first */
+
+/* Called with g_mu held, after `keep` was grown: drop least-recently-used families until the cache fits. */
+void evict_families(uint64_t keep) {
+    auto bytes = [] {
+        size_t b = 0;
+        for (auto &kv : g_families) b += kv.second.g.size() * PW * sizeof(uint64_t);
+        return b;
+    };
+    while (g_families.size() > 1 && bytes() > g_family_cap_bytes) {
+        auto lru = g_families.end();
+        for (auto it = g_families.begin(); it != g_families.end(); ++it)
+            if (it->first != keep && (lru == g_families.end() || it->second.last_use < lru->second.last_use)) lru = it;
+        if (lru == g_families.end()) break;
+        g_families.erase(lru);
+    }
+}
 
 void grow_family(Family &f, uint64_t stride, uint64_t count) {
     if (f.g.empty()) {
@@ -285,15 +304,22 @@ void grow_family(Family &f, uint64_t stride, uint64_t count) {
 
 bool mt_jump_ready() { return phi().ok; }
 
-bool mt_jump_polys(uint64_t stride, uint64_t count, std::vector<uint32_t> &bitmaps) {
+bool mt_jump_polys(uint64_t stride, uint64_t first, uint64_t count, std::vector<uint32_t> &bitmaps) {
     if (!phi().ok) return false;
     std::lock_guard<std::mutex> lk(g_mu);
     Family &f = g_families[stride];
-    grow_family(f, stride, count);
+    grow_family(f, stride, first + count);
+    f.last_use = ++g_tick;
+    evict_families(stride);
     bitmaps.resize((size_t)count * MTJ_POLY_WORDS);
     for (uint64_t c = 0; c < count; ++c)
-        memcpy(bitmaps.data() + (size_t)c * MTJ_POLY_WORDS, f.g[c].data(), sizeof(uint32_t) * MTJ_POLY_WORDS);
+        memcpy(bitmaps.data() + (size_t)c * MTJ_POLY_WORDS, f.g[first + c].data(), sizeof(uint32_t) * MTJ_POLY_WORDS);
     return true;
+}
+
+void mt_jump_set_host_cache_bytes(size_t bytes) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_family_cap_bytes = bytes;
 }
 
 static void apply_poly(const uint64_t *g, uint32_t *window);
@@ -303,6 +329,8 @@ bool mt_jump_host_family(uint32_t *window, uint64_t stride, uint64_t c) {
     std::lock_guard<std::mutex> lk(g_mu);
     Family &f = g_families[stride];
     grow_family(f, stride, c + 1);
+    f.last_use = ++g_tick;
+    evict_families(stride);
     apply_poly(f.g[c].data(), window);
     return true;
 }

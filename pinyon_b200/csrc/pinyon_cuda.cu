@@ -6,11 +6,19 @@
 
 #include <cuda_runtime.h>
 
+#include <dlfcn.h>
+#include <nccl.h> /* types and enums only: the library is dlopen'ed by pcu_create_multi, single-GPU use does not need it */
+
 #include <algorithm>
+#include <chrono>
+#include <condition_variable>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <functional>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "kernels.cuh"
@@ -43,7 +51,8 @@ constexpr int PIN_BASE_WINDOW = 1024; /* word offset in pin_small of the staged 
 
 enum BufId {
     B_STATE_SEED, B_STATE_POS, B_TSEED, B_DEPTH, B_BIAS, B_MSEED, B_PAYOFF, B_TRAJ, B_HASH, B_SUMS,
-    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_SEEDED, B_COUNT
+    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_SEEDED, B_PACKED, B_PAYTMP, B_WORDS,
+    B_COUNT
 };
 
 }  // namespace
@@ -69,7 +78,6 @@ struct pcu_ctx {
     int streams_per_sm = 0; /* model streams (generator warps) resident per SM; 0 = by batch size (run_stream) */
     int force_general = 0;
     int rb = 32;        /* rollouts per consumer batch of the fused kernels (32 or 64) */
-    int stream3 = 0;    /* fused path: k_stream3 (five role warps per stream) instead of k_stream2; measured slower (1.20 vs 1.11 ms) */
     int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
     bool small_attr[2] = {false, false};
     uint8_t *pin_out = nullptr; /* pinned staging for k_small's outputs (PIN_OUT_BYTES) */
@@ -91,6 +99,106 @@ struct pcu_ctx {
     /* cached fq table */
     uint32_t fq_w = 0;
     MtJump jump; /* host polynomials + device images for the model-stream jump-ahead */
+    /* statistics of the last rollout call (pcu_get_stat) */
+    uint64_t last_chunk = 0, last_streams = 0;
+    double last_family_ms = 0, last_table_ms = 0;
+    /* set by a multi-GPU parent around the call it hands to this (child) context: the child plays streams
+     * [first_stream, first_stream + its share) of ONE global family of model streams */
+    struct ShardHint {
+        bool active = false;
+        uint64_t chunk = 0;        /* rollouts per model stream, chosen for the whole batch */
+        uint64_t first_stream = 0; /* global index of this shard's first stream */
+        bool last = true;          /* owns the end of the batch: dumps the post-batch engine window */
+        bool keep_dev_sums = false; /* accumulate the counters in buf[B_SUMS] for the parent's reduction */
+        bool no_sync = false;      /* return after enqueueing; the parent synchronises */
+    } hint;
+    struct Multi *multi = nullptr; /* non-null: this context is a multi-GPU parent (pcu_create_multi) */
+};
+
+namespace {
+
+/* A thread that stays bound to one child context: launches for the GPUs of a sharded call are issued
+ * concurrently (a serial loop over eight devices would skew their start by ~0.3 ms). */
+class Worker {
+    std::thread th;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::function<void()> job;
+    bool has = false, quit = false, done = true;
+
+    void loop() {
+        std::unique_lock<std::mutex> lk(mu);
+        for (;;) {
+            cv.wait(lk, [&] { return has || quit; });
+            if (quit) return;
+            std::function<void()> f = std::move(job);
+            has = false;
+            lk.unlock();
+            f();
+            lk.lock();
+            done = true;
+            cv.notify_all();
+        }
+    }
+
+   public:
+    Worker() : th([this] { loop(); }) {}
+    ~Worker() {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            quit = true;
+        }
+        cv.notify_all();
+        th.join();
+    }
+    void start(std::function<void()> f) {
+        std::lock_guard<std::mutex> lk(mu);
+        job = std::move(f);
+        has = true;
+        done = false;
+        cv.notify_all();
+    }
+    void wait() {
+        std::unique_lock<std::mutex> lk(mu);
+        cv.wait(lk, [&] { return done; });
+    }
+};
+
+struct NcclApi {
+    void *lib = nullptr;
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool load() {
+        /* by SONAME: a process that already carries an NCCL (torch bundles one) shares it */
+        lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!lib) return false;
+        CommInitAll = reinterpret_cast<decltype(CommInitAll)>(dlsym(lib, "ncclCommInitAll"));
+        CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(lib, "ncclCommDestroy"));
+        AllReduce = reinterpret_cast<decltype(AllReduce)>(dlsym(lib, "ncclAllReduce"));
+        GroupStart = reinterpret_cast<decltype(GroupStart)>(dlsym(lib, "ncclGroupStart"));
+        GroupEnd = reinterpret_cast<decltype(GroupEnd)>(dlsym(lib, "ncclGroupEnd"));
+        GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(lib, "ncclGetErrorString"));
+        return CommInitAll && CommDestroy && AllReduce && GroupStart && GroupEnd && GetErrorString;
+    }
+};
+
+}  // namespace
+
+struct Multi {
+    std::vector<pcu_ctx *> kids;
+    std::vector<std::unique_ptr<Worker>> workers;
+    bool same_device = false; /* every child on one GPU (a test configuration): counters summed by k_sum_shards */
+    NcclApi nccl;
+    std::vector<ncclComm_t> comms;
+    std::vector<cudaEvent_t> ev_done; /* same_device: child streams -> child 0's stream */
+    uint64_t *pin_sums = nullptr;
+    uint64_t min_rollouts = 0; /* batches below this many rollouts go to the first GPU alone */
+    uint64_t nccl_calls = 0;
 };
 
 namespace {
@@ -320,44 +428,89 @@ int copy_back(pcu_ctx *ctx, int mem, T *dst, const T *dev, uint64_t count) {
 
 struct OutDev {
     bool payoff_direct = false; /* payoff points at the caller's pinned host buffer (zero-copy stores) */
+    bool packed_direct = false;
     uint8_t *payoff = nullptr;
+    uint8_t *packed = nullptr; /* 2-bit payoffs, four rollouts per byte */
     uint8_t *traj = nullptr;
     uint32_t *hash = nullptr;
     unsigned long long *sums = nullptr;
 };
 
+/* Device-visible address of a pinned host buffer, for kernels that store their output straight over PCIe. */
+uint8_t *zero_copy_pointer(void *host) {
+    cudaPointerAttributes at;
+    uint8_t *dev = nullptr;
+    if (cudaPointerGetAttributes(&at, host) == cudaSuccess && at.type == cudaMemoryTypeHost && at.devicePointer)
+        dev = static_cast<uint8_t *>(at.devicePointer);
+    cudaGetLastError(); /* pageable memory reports an error on some drivers: not ours */
+    return dev;
+}
+
 int prepare_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, OutDev &od) {
     int rc;
     /* Large batches into PINNED host memory: the kernels store the payoff bytes straight into the caller's
      * buffer over PCIe while they run, instead of a device buffer + a D2H copy after the last rollout. */
-    od.payoff_direct = false;
-    if (ctx->zero_copy && out->mem == PCU_MEM_HOST && out->payoff_x2 && n >= (1ull << 20)) {
-        cudaPointerAttributes at;
-        if (cudaPointerGetAttributes(&at, out->payoff_x2) == cudaSuccess && at.type == cudaMemoryTypeHost &&
-            at.devicePointer) {
-            od.payoff = static_cast<uint8_t *>(at.devicePointer);
-            od.payoff_direct = true;
-        }
-        cudaGetLastError(); /* pageable memory reports an error on some drivers: not ours */
-    }
+    od.payoff_direct = od.packed_direct = false;
+    const bool direct_ok = ctx->zero_copy && out->mem == PCU_MEM_HOST && n >= (1ull << 20);
+    /* with a packed output the byte payoffs stay in HBM: the packing kernel of the general paths reads them */
+    if (direct_ok && out->payoff_x2 && !out->payoff_packed2 && (od.payoff = zero_copy_pointer(out->payoff_x2)))
+        od.payoff_direct = true;
+    if (direct_ok && out->payoff_packed2 && (od.packed = zero_copy_pointer(out->payoff_packed2))) od.packed_direct = true;
     if (!od.payoff_direct && (rc = stage_out(ctx, out->mem, out->payoff_x2, n, B_PAYOFF, &od.payoff))) return rc;
+    if (!od.packed_direct && (rc = stage_out(ctx, out->mem, out->payoff_packed2, (n + 3) / 4, B_PACKED, &od.packed)))
+        return rc;
     if ((rc = stage_out(ctx, out->mem, out->traj, n * (uint64_t)out->traj_stride * 3, B_TRAJ, &od.traj)))
         return rc;
     if ((rc = stage_out(ctx, out->mem, out->traj_hash, n, B_HASH, &od.hash))) return rc;
     uint64_t *s = nullptr;
-    if ((rc = stage_out(ctx, out->mem, out->sums, (uint64_t)8, B_SUMS, &s))) return rc;
+    if (ctx->hint.keep_dev_sums) {
+        CU(ctx->buf[B_SUMS].ensure(8 * sizeof(uint64_t)));
+        s = reinterpret_cast<uint64_t *>(ctx->buf[B_SUMS].p);
+    } else if ((rc = stage_out(ctx, out->mem, out->sums, (uint64_t)8, B_SUMS, &s))) {
+        return rc;
+    }
     od.sums = reinterpret_cast<unsigned long long *>(s);
     if (od.sums) CU(cudaMemsetAsync(od.sums, 0, 8 * sizeof(uint64_t), ctx->stream));
+    return PCU_OK;
+}
+
+__global__ void k_pack2(const uint8_t *__restrict__ pay, uint8_t *__restrict__ packed, uint64_t n) {
+    const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; /* output byte = rollouts 4q .. 4q + 3 */
+    if (4 * q >= n) return;
+    uint32_t v = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+        if (4 * q + j < n) v |= (uint32_t)(pay[4 * q + j] & 3u) << (2 * j);
+    packed[q] = (uint8_t)v;
+}
+
+/* General paths write payoff bytes; a packed output is made from them by one more pass over HBM. */
+int pack_source(pcu_ctx *ctx, OutDev &od, uint64_t n, uint8_t **pay) {
+    *pay = od.payoff;
+    if (od.packed && !od.payoff) {
+        CU(ctx->buf[B_PAYTMP].ensure(n));
+        *pay = reinterpret_cast<uint8_t *>(ctx->buf[B_PAYTMP].p);
+    }
+    return PCU_OK;
+}
+int pack_after(pcu_ctx *ctx, const OutDev &od, uint64_t n, const uint8_t *pay) {
+    if (!od.packed || !n) return PCU_OK;
+    k_pack2<<<(unsigned)(((n + 3) / 4 + 255) / 256), 256, 0, ctx->stream>>>(pay, od.packed, n);
+    ctx->launches++;
+    CU(cudaGetLastError());
     return PCU_OK;
 }
 
 int finish_out(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od) {
     int rc;
     if (!od.payoff_direct && (rc = copy_back(ctx, out->mem, out->payoff_x2, od.payoff, n))) return rc;
+    if (!od.packed_direct && (rc = copy_back(ctx, out->mem, out->payoff_packed2, od.packed, (n + 3) / 4))) return rc;
     if ((rc = copy_back(ctx, out->mem, out->traj, od.traj, n * (uint64_t)out->traj_stride * 3))) return rc;
     if ((rc = copy_back(ctx, out->mem, out->traj_hash, od.hash, n))) return rc;
-    if ((rc = copy_back(ctx, out->mem, out->sums, reinterpret_cast<const uint64_t *>(od.sums), (uint64_t)8)))
+    if (!ctx->hint.keep_dev_sums &&
+        (rc = copy_back(ctx, out->mem, out->sums, reinterpret_cast<const uint64_t *>(od.sums), (uint64_t)8)))
         return rc;
+    if (ctx->hint.no_sync) return PCU_OK; /* the multi-GPU parent synchronises every shard after its reduction */
     CU(cudaStreamSynchronize(ctx->stream));
     return PCU_OK;
 }
@@ -370,6 +523,7 @@ int finish_all(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od, p
         ctx->engine_pending = false;
         return rc;
     }
+    if (ctx->hint.no_sync) return PCU_OK; /* engine_pending stays set: the parent reads pin_small after its sync */
     if (ctx->engine_pending) {
         engine_from_window(ctx->pin_small, rng->mt_x, rng->mt_p);
         ctx->engine_pending = false;
@@ -381,16 +535,17 @@ int finish_all(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od, p
 
 /* Fill B_CKPT with `count` windows: window c holds the 624 raw words preceding model
  * draw number c * stride, counted from the engine's next draw. */
-int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t count, uint64_t stride) {
+int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t first, uint64_t count, uint64_t stride) {
     uint32_t *win = ctx->pin_small + PIN_BASE_WINDOW; /* pinned: the upload below needs no host sync */
     host_window_from_engine(mt_x, mt_p, win);
     CU(ctx->buf[B_CKPT].ensure(sizeof(uint32_t) * MT_N * (count + 1)));
     CU(ctx->buf[B_ENDWIN].ensure(sizeof(uint32_t) * MT_N));
     uint32_t *d_ck = reinterpret_cast<uint32_t *>(ctx->buf[B_CKPT].p);
-    if (ctx->host_checkpoints && count > 1) {
+    if (ctx->host_checkpoints && (count > 1 || first > 0)) {
         /* test hook: plain stepping on the host, the definition the jump kernels must match */
         std::vector<uint32_t> all((size_t)MT_N * count);
         std::vector<uint32_t> w(win, win + MT_N);
+        for (uint64_t c = 0; c < first; ++c) host_window_advance(w.data(), stride);
         for (uint64_t c = 0; c < count; ++c) {
             memcpy(all.data() + (size_t)MT_N * c, w.data(), sizeof(uint32_t) * MT_N);
             if (c + 1 < count) host_window_advance(w.data(), stride);
@@ -400,8 +555,9 @@ int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t
         return PCU_OK;
     }
     std::string jerr;
-    if (ctx->jump.run(ctx->stream, ctx->sms, win, count, stride, d_ck, &ctx->launches, &jerr) != 0)
+    if (ctx->jump.run(ctx->stream, ctx->sms, win, first, count, stride, d_ck, &ctx->launches, &jerr) != 0)
         return fail(ctx, PCU_ERR_CUDA, "jump-ahead failed: %s", jerr.c_str());
+    ctx->last_family_ms += ctx->jump.last_build_ms;
     return PCU_OK;
 }
 
@@ -433,17 +589,12 @@ uint64_t pick_chunk(uint64_t units, uint64_t slots, uint64_t min_chunk) {
     return m << e;
 }
 
-template <int KIND, typename CodeT>
-int launch_stream3(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t smem) {
-    auto kern = tab_smem ? k_stream3<KIND, CodeT, true> : k_stream3<KIND, CodeT, false>;
-    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    kern<<<P.streams, S3_THREADS, smem, ctx->stream>>>(P);
-    CU(cudaEventRecord(ctx->ev1, ctx->stream));
-    ctx->ev_valid = true;
-    ctx->launches++;
-    CU(cudaGetLastError());
-    return PCU_OK;
+/* Rollouts per model stream of a uniform-depth batch: a multiple of 128, so that every stream starts on a
+ * boundary of the consumers' vector stores (four payoff bytes / one packed byte per lane) and a multi-GPU
+ * shard — a whole number of streams — starts on a byte of the packed output. */
+uint64_t pick_rollout_chunk(uint64_t n, uint64_t slots, uint64_t min_chunk) {
+    const uint64_t c = pick_chunk(n, slots, std::max<uint64_t>(min_chunk, 128));
+    return (c + 127) & ~127ull;
 }
 
 template <int KIND, typename CodeT>
@@ -471,44 +622,44 @@ bool stream_fits(uint32_t depth, uint64_t actions) {
     return smem <= SMEM_LIMIT;
 }
 
+/* Model streams (generator warps) resident per SM for a uniform-depth batch of n rollouts on this GPU.  Every
+ * stream costs one jump-ahead checkpoint (~0.5 us of the whole GPU) and a second generator warp per scheduler
+ * hides the first one's fixed-latency stalls: worth it from ~2.5e8 rollout-steps per call on
+ * (tools/sweep_stream.py: config B 2.78 -> 2.52 ms at 8 per SM, config A 1.41 -> 1.53 ms). */
+int streams_per_sm_for(const pcu_ctx *ctx, uint64_t n, uint32_t depth) {
+    return ctx->streams_per_sm ? ctx->streams_per_sm : ((double)n * depth >= 2.5e8 ? 8 : 4);
+}
+
 /* Fused path (mode S, uniform depth, shared or absent state stream). */
 template <int KIND>
-int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od) {
+int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng, const OutDev &od, const pcu_out *out) {
     const uint64_t n = P.n;
-    /* Every stream costs one jump-ahead checkpoint (~0.5 us of the whole GPU) and a second generator warp per
-     * scheduler hides the first one's fixed-latency stalls: worth it from ~2.5e8 rollout-steps per call on
-     * (tools/sweep_stream.py: config B 2.78 -> 2.52 ms at 8 per SM, config A 1.41 -> 1.53 ms). */
-    const int per_sm = ctx->streams_per_sm ? ctx->streams_per_sm : ((double)n * P.depth >= 2.5e8 ? 8 : 4);
-    const uint64_t slots = (uint64_t)ctx->sms * per_sm;
-    P.chunk = pick_chunk(n, slots, 128);
+    uint64_t first_stream = 0;
+    if (ctx->hint.active) { /* one shard of a multi-GPU batch: the parent chose the streams */
+        P.chunk = ctx->hint.chunk;
+        first_stream = ctx->hint.first_stream;
+    } else {
+        P.chunk = pick_rollout_chunk(n, (uint64_t)ctx->sms * streams_per_sm_for(ctx, n, P.depth), 128);
+    }
     P.streams = (uint32_t)((n + P.chunk - 1) / P.chunk);
-    P.rb = ctx->rb;
+    ctx->last_chunk = P.chunk;
+    ctx->last_streams = P.streams;
+    P.rb = od.packed ? 128 : ctx->rb; /* the packed output is one byte per lane: four consecutive rollouts */
     P.qlen = 1024;
     while (P.qlen < 2ull * P.rb * P.depth + 2 * GW_PASS_STEPS) P.qlen <<= 1;
-    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, P.streams, 4ull * P.depth * P.chunk);
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, first_stream, P.streams, 4ull * P.depth * P.chunk);
     if (rc) return rc;
     P.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
-    P.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
+    const bool want_end = !ctx->hint.active || ctx->hint.last;
+    P.end_window = want_end ? reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p) : nullptr;
     P.payoff = od.payoff;
+    P.payoff_packed2 = od.packed;
     P.traj = od.traj;
     P.traj_hash = od.hash;
     P.sums = od.sums;
+    P.vec_ok = (P.chunk % 4 == 0) && ((uintptr_t)od.payoff % 4 == 0) && ((uintptr_t)od.hash % 16 == 0);
+    (void)out;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
-    if (ctx->stream3) { /* one CTA of three warps per stream (k_stream3) */
-        size_t smem3 = 64 + (size_t)GW_RING * 4 + S3_RAWQ_U4 * 16 + (size_t)(P.qlen + 16) * (code8 ? 1 : 2) + 16;
-        const size_t tab3 = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
-        bool tab_smem3 = false;
-        if (KIND == KIND_TREE && smem3 + tab3 + 16 <= 48 * 1024) { /* keep four CTAs per SM */
-            tab_smem3 = true;
-            smem3 += tab3 + 16;
-        }
-        if (code8)
-            rc = launch_stream3<KIND, uint8_t>(ctx, P, tab_smem3, smem3);
-        else
-            rc = launch_stream3<KIND, uint16_t>(ctx, P, tab_smem3, smem3);
-        if (rc) return rc;
-        return fetch_end_window(ctx);
-    }
     const size_t queue_bytes = (size_t)GW_PAIRS * (P.qlen + 16) * (code8 ? 1 : 2);
     size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + queue_bytes + 16;
     const size_t tab_bytes = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
@@ -523,20 +674,34 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     else
         rc = launch_stream<KIND, uint16_t>(ctx, P, tab_smem, smem);
     if (rc) return rc;
-    return fetch_end_window(ctx);
+    return want_end ? fetch_end_window(ctx) : PCU_OK;
 }
 
-/* General path helper: joint action codes for every step of a mode-S batch. */
-int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, pcu_model_rng *rng, bool *code16) {
+/* General path helper: joint action codes for every step of a mode-S batch.  `uniform_depth` > 0: every rollout
+ * plays that many steps, and the streams are whole numbers of rollouts (so that a multi-GPU shard is a whole
+ * number of streams of one global family); 0: ragged depths, streams are cut by steps. */
+int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, pcu_model_rng *rng, bool *code16,
+              uint32_t uniform_depth = 0, uint64_t n = 0) {
     const bool c16 = (uint64_t)rows * cols > 256;
     *code16 = c16;
     const uint64_t slots = (uint64_t)ctx->sms * (ctx->streams_per_sm ? ctx->streams_per_sm : 4);
-    const uint64_t chunk = pick_chunk(total_steps ? total_steps : 1, slots, 4096); /* steps per stream */
+    uint64_t chunk, first_stream = 0; /* chunk in steps */
+    if (uniform_depth && ctx->hint.active) {
+        chunk = ctx->hint.chunk * uniform_depth;
+        first_stream = ctx->hint.first_stream;
+    } else if (uniform_depth) {
+        chunk = pick_rollout_chunk(n, slots, (4096 + uniform_depth - 1) / uniform_depth) * uniform_depth;
+    } else {
+        chunk = pick_chunk(total_steps ? total_steps : 1, slots, 4096);
+    }
     uint64_t streams = (total_steps + chunk - 1) / chunk;
     if (streams == 0) streams = 1;
-    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, streams, 4ull * chunk);
+    ctx->last_chunk = chunk;
+    ctx->last_streams = streams;
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, first_stream, streams, 4ull * chunk);
     if (rc) return rc;
     CU(ctx->buf[B_CODES].ensure((total_steps + 8) * (c16 ? 2 : 1)));
+    const bool want_end = !ctx->hint.active || ctx->hint.last;
     Gen2Params G;
     G.total_steps = total_steps;
     G.chunk_steps = chunk;
@@ -546,7 +711,7 @@ int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, 
     G.mcol = make_fold_const(cols);
     G.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
     G.codes = ctx->buf[B_CODES].p;
-    G.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
+    G.end_window = want_end ? reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p) : nullptr;
     if (total_steps == 0) return PCU_OK; /* engine untouched */
     const unsigned ctas = (unsigned)((streams + 3) / 4);
     if (c16)
@@ -555,7 +720,7 @@ int gen_codes(pcu_ctx *ctx, uint64_t total_steps, uint32_t rows, uint32_t cols, 
         k_gen_codes2<uint8_t><<<ctas, 128, 0, ctx->stream>>>(G);
     ctx->launches++;
     CU(cudaGetLastError());
-    return fetch_end_window(ctx);
+    return want_end ? fetch_end_window(ctx) : PCU_OK;
 }
 
 /* Exclusive prefix sum of per-rollout depths -> first step of each rollout. */
@@ -805,9 +970,14 @@ int run_small(pcu_ctx *ctx, SmallParams &SP, uint32_t n, pcu_model_rng *rng, con
     /* the host engine moves on while the kernel runs: 4 draws per step (monte-carlo-model.hh:89-90) */
     uint64_t steps = 0;
     for (uint32_t i = 0; i < n; ++i) steps += SP.x.depth[i];
-    int rc = pcu_mt_discard(rng->mt_x, rng->mt_p, 4 * steps);
+    /* into a copy: the caller's engine moves only once the kernel is known to have succeeded, as on every other path */
+    uint32_t next_x[MT_N], next_p = *rng->mt_p;
+    memcpy(next_x, rng->mt_x, sizeof(next_x));
+    int rc = pcu_mt_discard(next_x, &next_p, 4 * steps);
     CU(cudaStreamSynchronize(ctx->stream));
     if (rc) return rc;
+    memcpy(rng->mt_x, next_x, sizeof(next_x));
+    *rng->mt_p = next_p;
     const uint32_t *hash = reinterpret_cast<const uint32_t *>(ctx->pin_out + PIN_OUT_HASH);
     if (out->payoff_x2) memcpy(out->payoff_x2, ctx->pin_out, n);
     if (out->traj_hash) memcpy(out->traj_hash, hash, sizeof(uint32_t) * n);
@@ -896,6 +1066,23 @@ int pcu_create(int device_id, pcu_ctx **out) {
 
 void pcu_destroy(pcu_ctx *ctx) {
     if (!ctx) return;
+    if (ctx->multi) {
+        Multi *M = ctx->multi;
+        for (pcu_ctx *kid : M->kids) {
+            cudaSetDevice(kid->device);
+            cudaStreamSynchronize(kid->stream);
+        }
+        for (ncclComm_t c : M->comms)
+            if (c) M->nccl.CommDestroy(c);
+        M->workers.clear();
+        for (cudaEvent_t e : M->ev_done)
+            if (e) cudaEventDestroy(e);
+        for (pcu_ctx *kid : M->kids) pcu_destroy(kid);
+        if (M->pin_sums) cudaFreeHost(M->pin_sums);
+        delete M;
+        delete ctx;
+        return;
+    }
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     for (auto &b : ctx->buf) b.release();
@@ -912,9 +1099,20 @@ void pcu_destroy(pcu_ctx *ctx) {
 
 const char *pcu_last_error(const pcu_ctx *ctx) { return ctx ? ctx->err.c_str() : "null context"; }
 const char *pcu_last_path(const pcu_ctx *ctx) { return ctx ? ctx->path.c_str() : ""; }
-uint64_t pcu_kernel_launches(const pcu_ctx *ctx) { return ctx ? ctx->launches : 0; }
+uint64_t pcu_kernel_launches(const pcu_ctx *ctx) {
+    if (!ctx) return 0;
+    uint64_t total = ctx->launches;
+    if (ctx->multi)
+        for (const pcu_ctx *kid : ctx->multi->kids) total += kid->launches;
+    return total;
+}
 
 double pcu_last_kernel_ms(pcu_ctx *ctx) {
+    if (ctx && ctx->multi) { /* the slowest shard */
+        double worst = -1.0;
+        for (pcu_ctx *kid : ctx->multi->kids) worst = std::max(worst, pcu_last_kernel_ms(kid));
+        return worst;
+    }
     if (!ctx || !ctx->ev_valid) return -1.0;
     float ms = 0;
     if (cudaEventSynchronize(ctx->ev1) != cudaSuccess || cudaEventElapsedTime(&ms, ctx->ev0, ctx->ev1) != cudaSuccess)
@@ -924,12 +1122,41 @@ double pcu_last_kernel_ms(pcu_ctx *ctx) {
 
 int pcu_set_stream(pcu_ctx *ctx, void *cuda_stream) {
     if (!ctx) return PCU_ERR_INVALID;
+    if (ctx->multi) {
+        if (ctx->multi->kids.size() == 1) return pcu_set_stream(ctx->multi->kids[0], cuda_stream);
+        return fail(ctx, PCU_ERR_INVALID, "a multi-GPU context runs on its own streams");
+    }
     ctx->stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
     return PCU_OK;
 }
 
 int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     if (!ctx || !key) return PCU_ERR_INVALID;
+    if (ctx->multi) {
+        if (!strcmp(key, "multi_min_rollouts")) {
+            if (value < 0) return PCU_ERR_INVALID;
+            ctx->multi->min_rollouts = (uint64_t)value;
+            return PCU_OK;
+        }
+        for (pcu_ctx *kid : ctx->multi->kids) {
+            const int rc = pcu_set_option(kid, key, value);
+            if (rc) {
+                ctx->err = kid->err;
+                return rc;
+            }
+        }
+        return PCU_OK;
+    }
+    if (!strcmp(key, "jump_families")) {
+        if (value < 1 || value > 1024) return fail(ctx, PCU_ERR_INVALID, "jump_families must be 1..1024");
+        ctx->jump.max_families = (size_t)value;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "jump_host_cache_mb")) {
+        if (value < 1) return PCU_ERR_INVALID;
+        mt_jump_set_host_cache_bytes((size_t)value << 20);
+        return PCU_OK;
+    }
     if (!strcmp(key, "streams_per_sm") || !strcmp(key, "ctas_per_sm")) { /* second name: r1a spelling */
         if (value < 0 || value > 16) return fail(ctx, PCU_ERR_INVALID, "streams_per_sm must be 0 (auto) or 1..16");
         ctx->streams_per_sm = (int)value;
@@ -944,12 +1171,8 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
         return PCU_OK;
     }
     if (!strcmp(key, "rb")) {
-        if (value != 32 && value != 64) return PCU_ERR_INVALID;
+        if (value != 32 && value != 64 && value != 128) return PCU_ERR_INVALID;
         ctx->rb = (int)value;
-        return PCU_OK;
-    }
-    if (!strcmp(key, "stream3")) {
-        ctx->stream3 = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "small_path")) {
@@ -975,7 +1198,8 @@ void *pcu_host_alloc(pcu_ctx *ctx, size_t bytes) {
     if (!ctx) return nullptr;
     void *p = nullptr;
     cudaSetDevice(ctx->device);
-    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+    /* portable + mapped: every GPU of a multi-GPU context may store its shard's payoffs straight into it */
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable | cudaHostAllocMapped) != cudaSuccess) return nullptr;
     return p;
 }
 void pcu_host_free(pcu_ctx *ctx, void *p) {
@@ -1024,10 +1248,18 @@ int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint6
     return PCU_OK;
 }
 
-int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
+}  // extern "C"
+
+namespace {
+
+/* One GPU's share of the work: everything below runs on ctx->device. */
+int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
     int rc = check_common(ctx, b, rng, out);
     if (rc) return rc;
     ctx->err.clear();
+    ctx->engine_pending = false; /* a call that failed midway must not hand its window to this one */
+    ctx->last_chunk = ctx->last_streams = 0;
+    ctx->last_family_ms = ctx->last_table_ms = 0;
     if (b->mem != PCU_MEM_HOST && b->mem != PCU_MEM_DEVICE) return fail(ctx, PCU_ERR_INVALID, "bad batch->mem");
     if (b->mem != out->mem) return fail(ctx, PCU_ERR_INVALID, "batch and out must share a memory space");
     if (b->rows < 1 || b->cols < 1 || b->rows > 255 || b->cols > 255)
@@ -1048,8 +1280,8 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     if (out->traj && out->traj_stride < (b->depth ? 1u : b->depth_u))
         return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
     CU(cudaSetDevice(ctx->device));
-    if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST &&
-        rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
+    if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST && !out->payoff_packed2 &&
+        !ctx->hint.no_sync && rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
         static thread_local SmallParams SP; /* ~3.6 KB: kept off the stack of recursive searches */
         memset(&SP.w, 0, sizeof(SP.w));
         SP.w.rows = b->rows;
@@ -1120,12 +1352,27 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     }
     if (fused) {
         if (defer_inputs && (rc = inputs_ready(ctx))) return rc;
-        const uint32_t tab_base = pos_min - gen_words;
-        const uint32_t tab_len = (uint32_t)span;
+        uint32_t tab_base = pos_min - gen_words;
+        uint32_t tab_len = (uint32_t)span;
         const double pu = (T > 1) ? host_uniform_from_seed(b->transition_seed_u) : 0.0;
         auto &key = ctx->tab_key;
-        if (!(key.valid && key.seed == (uint32_t)b->state_seed_u && key.base == tab_base && key.len == tab_len &&
-              key.T == T && key.pu == pu && key.thr_p == b->thr_p && key.thr_q == b->thr_q)) {
+        const bool same_stream = key.valid && key.seed == (uint32_t)b->state_seed_u && key.T == T && key.pu == pu &&
+                                 key.thr_p == b->thr_p && key.thr_q == b->thr_q;
+        if (same_stream && key.base <= tab_base && (uint64_t)key.base + key.len >= (uint64_t)tab_base + tab_len) {
+            /* the cached table COVERS this batch (leaf batches of one search move their position range from call
+             * to call): no rebuild, no upload */
+            tab_base = key.base;
+            tab_len = key.len;
+        } else {
+            const auto t0 = std::chrono::steady_clock::now();
+            if (same_stream) { /* grow to the union, so that a search's table settles after a few batches */
+                const uint64_t lo = std::min<uint64_t>(key.base, tab_base);
+                const uint64_t hi = std::max<uint64_t>((uint64_t)key.base + key.len, (uint64_t)tab_base + tab_len);
+                if (hi - lo <= (1u << 16)) {
+                    tab_base = (uint32_t)lo;
+                    tab_len = (uint32_t)(hi - lo);
+                }
+            }
             std::vector<uint8_t> tab;
             host_build_table(b->state_seed_u, tab_base, tab_len, T, pu, b->thr_p, b->thr_q, tab);
             CU(ctx->buf[B_TAB].ensure(tab.size()));
@@ -1139,6 +1386,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
             key.pu = pu;
             key.thr_p = b->thr_p;
             key.thr_q = b->thr_q;
+            ctx->last_table_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         }
         Stream2Params P;
         memset(&P, 0, sizeof(P));
@@ -1158,7 +1406,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         P.bias_u = b->payoff_bias_u;
         P.traj_stride = out->traj_stride;
         ctx->path = "stream_table";
-        if ((rc = run_stream<KIND_TREE>(ctx, P, b->rows, rng, od))) return rc;
+        if ((rc = run_stream<KIND_TREE>(ctx, P, b->rows, rng, od, out))) return rc;
         return finish_all(ctx, out, n, od, rng);
     }
 
@@ -1186,7 +1434,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     W.thr_q = b->thr_q;
     W.fq = d_fq;
     W.fq_w = fq_w;
-    W.payoff = od.payoff;
+    if ((rc = pack_source(ctx, od, n, &W.payoff))) return rc;
     W.traj = od.traj;
     W.traj_stride = out->traj_stride;
     W.traj_hash = od.hash;
@@ -1199,7 +1447,7 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
             if ((rc = scan_depths(ctx, d_depth, n, &W.step_off, &total_steps))) return rc;
         }
         bool c16;
-        if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16))) return rc;
+        if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16, d_depth ? 0u : (uint32_t)b->depth_u, n))) return rc;
         W.codes = ctx->buf[B_CODES].p;
         W.code_u16 = c16;
     } else {
@@ -1211,13 +1459,13 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
     uint64_t lane_words = 0, lane_dmax = 0;
     LaneGeom geom;
     bool lane = !ctx->force_warp && T == 1;
-    if (lane) {
-        const uint32_t per_step = gen_words + b->rows * b->cols - 1 + 2;
+    if (lane || d_pos) { /* per-rollout positions are range-checked on every path (k_warp would index its engine below 0) */
+        const uint32_t per_step = gen_words + b->rows * b->cols * T - 1 + 2;
         if ((rc = lane_bound(ctx, n, d_pos, b->state_pos_u, d_depth, b->depth_u, gen_words, per_step, &lane_words,
                              &lane_dmax, &geom.pos_min, &geom.pos_max)))
             return rc;
-        lane = lane_words <= MT_N - 1 && (rng->mode == PCU_MODEL_STREAM || 4 * lane_dmax <= MT_LAG - 3) &&
-               geom.pos_min >= gen_words;
+        if (geom.pos_min < gen_words) return fail(ctx, PCU_ERR_INVALID, "a state_pos is below 2*rows*cols*transitions");
+        lane = lane && lane_words <= MT_N - 1 && (rng->mode == PCU_MODEL_STREAM || 4 * lane_dmax <= MT_LAG - 3);
         geom.words = (uint32_t)lane_words;
         geom.dmax = (uint32_t)lane_dmax;
     }
@@ -1229,13 +1477,17 @@ int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *
         rc = lane ? launch_lane<KIND_TREE, 1>(ctx, W, geom) : launch_warp<KIND_TREE, 1>(ctx, W);
     }
     if (rc) return rc;
+    if ((rc = pack_after(ctx, od, n, W.payoff))) return rc;
     return finish_all(ctx, out, n, od, rng);
 }
 
-int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_out *out) {
+int rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_out *out) {
     int rc = check_common(ctx, b, rng, out);
     if (rc) return rc;
     ctx->err.clear();
+    ctx->engine_pending = false; /* a call that failed midway must not hand its window to this one */
+    ctx->last_chunk = ctx->last_streams = 0;
+    ctx->last_family_ms = ctx->last_table_ms = 0;
     if (b->mem != PCU_MEM_HOST && b->mem != PCU_MEM_DEVICE) return fail(ctx, PCU_ERR_INVALID, "bad batch->mem");
     if (b->mem != out->mem) return fail(ctx, PCU_ERR_INVALID, "batch and out must share a memory space");
     if (b->n_actions < 1 || b->n_actions > 255) return fail(ctx, PCU_ERR_INVALID, "n_actions must be 1..255");
@@ -1243,8 +1495,8 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
     const uint64_t n = b->n;
     CU(cudaSetDevice(ctx->device));
-    if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST &&
-        rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
+    if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST && !out->payoff_packed2 &&
+        !ctx->hint.no_sync && rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
         static thread_local SmallParams SP;
         memset(&SP.w, 0, sizeof(SP.w));
         SP.w.rows = SP.w.cols = b->n_actions;
@@ -1278,7 +1530,7 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         P.mcol = make_fold_const(b->n_actions);
         P.traj_stride = out->traj_stride;
         ctx->path = "stream_mold";
-        if ((rc = run_stream<KIND_MOLD>(ctx, P, b->n_actions, rng, od))) return rc;
+        if ((rc = run_stream<KIND_MOLD>(ctx, P, b->n_actions, rng, od, out))) return rc;
         return finish_all(ctx, out, n, od, rng);
     }
     WarpParams W;
@@ -1291,7 +1543,7 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
     W.mcol = make_mod_const(b->n_actions);
     W.depth = d_depth;
     W.depth_u = b->depth_u;
-    W.payoff = od.payoff;
+    if ((rc = pack_source(ctx, od, n, &W.payoff))) return rc;
     W.traj = od.traj;
     W.traj_stride = out->traj_stride;
     W.traj_hash = od.hash;
@@ -1302,7 +1554,8 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
             if ((rc = scan_depths(ctx, d_depth, n, &W.step_off, &total_steps))) return rc;
         }
         bool c16;
-        if ((rc = gen_codes(ctx, total_steps, b->n_actions, b->n_actions, rng, &c16))) return rc;
+        if ((rc = gen_codes(ctx, total_steps, b->n_actions, b->n_actions, rng, &c16, d_depth ? 0u : (uint32_t)b->depth_u, n)))
+            return rc;
         W.codes = ctx->buf[B_CODES].p;
         W.code_u16 = c16;
         ctx->path = "warp_mold_S";
@@ -1318,11 +1571,392 @@ int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, 
         rc = lane ? launch_lane<KIND_MOLD, 1>(ctx, W, geom) : launch_warp<KIND_MOLD, 1>(ctx, W);
         if (rc) return rc;
     }
+    if ((rc = pack_after(ctx, od, n, W.payoff))) return rc;
     return finish_all(ctx, out, n, od, rng);
+}
+
+/* ------------------------------------------------------------------ multi-GPU parent (pcu_create_multi) */
+
+}  // namespace
+
+namespace {
+
+struct SumPtrs {
+    const unsigned long long *p[16];
+    int n;
+};
+__global__ void k_sum_shards(SumPtrs S, unsigned long long *out) {
+    const int t = threadIdx.x;
+    if (t < 8) {
+        unsigned long long v = 0;
+        for (int g = 0; g < S.n; ++g) v += S.p[g][t];
+        out[t] = v;
+    }
+}
+
+struct ShardPlan {
+    uint64_t first = 0, count = 0;   /* rollouts [first, first + count) */
+    uint64_t first_stream = 0;       /* uniform depth, mode S: global index of the shard's first model stream */
+    uint64_t words_before = 0;       /* ragged depth, mode S: model draws consumed by the rollouts before `first` */
+    bool last = false;
+};
+
+/* Cut a batch into contiguous rollout-index shards.  Uniform depth in mode S: the batch is ONE
+ * family of model streams of `chunk` rollouts each (stride 4 * depth * chunk draws) and a shard is a whole number of
+ * them, so GPU g applies polynomials x^((g * spg + j) * stride) to the caller's engine window itself — no host-side
+ * jump per shard.  Ragged depth: equal rollout counts; the shard's engine is the caller's advanced on the host by
+ * 4 * (steps of the rollouts before it).  Mode P: equal rollout counts, nothing else. */
+void plan_shards(const Multi &M, uint64_t n, int mode, const uint16_t *depth, uint32_t depth_u, uint64_t *chunk_out,
+                 std::vector<ShardPlan> &plan) {
+    const size_t G = M.kids.size();
+    plan.assign(G, ShardPlan{});
+    *chunk_out = 0;
+    if (mode == PCU_MODEL_STREAM && !depth) {
+        const pcu_ctx *k0 = M.kids[0];
+        uint64_t slots = 0;
+        for (const pcu_ctx *k : M.kids) slots += (uint64_t)k->sms * streams_per_sm_for(k0, n / G, depth_u);
+        const uint64_t min_chunk = std::max<uint64_t>(128, (4096 + depth_u - 1) / std::max<uint32_t>(depth_u, 1));
+        const uint64_t chunk = pick_rollout_chunk(n, slots, min_chunk);
+        const uint64_t S = (n + chunk - 1) / chunk, spg = (S + G - 1) / G;
+        *chunk_out = chunk;
+        for (size_t g = 0; g < G; ++g) {
+            const uint64_t s0 = std::min<uint64_t>(S, g * spg), s1 = std::min<uint64_t>(S, s0 + spg);
+            plan[g].first_stream = s0;
+            plan[g].first = std::min<uint64_t>(n, s0 * chunk);
+            plan[g].count = std::min<uint64_t>(n, s1 * chunk) - plan[g].first;
+            plan[g].last = s1 == S && s0 < S;
+        }
+        return;
+    }
+    const uint64_t per = ((n + G - 1) / G + 3) & ~3ull; /* multiples of four: a shard starts on a byte of the packed output */
+    uint64_t words = 0, next = 0;
+    for (size_t g = 0; g < G; ++g) {
+        plan[g].first = std::min<uint64_t>(n, g * per);
+        plan[g].count = std::min<uint64_t>(n, plan[g].first + per) - plan[g].first;
+        if (mode == PCU_MODEL_STREAM) { /* ragged: prefix of the depths up to the shard (host memory) */
+            for (; next < plan[g].first; ++next) words += 4ull * depth[next];
+            plan[g].words_before = words;
+        }
+    }
+    for (size_t g = G; g-- > 0;)
+        if (plan[g].count) {
+            plan[g].last = true;
+            break;
+        }
+}
+
+template <typename T>
+const T *off(const T *p, uint64_t k) {
+    return p ? p + k : nullptr;
+}
+template <typename T>
+T *off(T *p, uint64_t k) {
+    return p ? p + k : nullptr;
+}
+
+/* Run `call(kid, g)` for every non-empty shard on the workers, then reduce the counters over the GPUs (NCCL
+ * all-reduce of eight u64 — the path's only collective), synchronise, and hand back the post-batch engine. */
+template <typename Call>
+int multi_dispatch(pcu_ctx *ctx, const std::vector<ShardPlan> &plan, uint64_t chunk, pcu_model_rng *rng, pcu_out *out,
+                   std::vector<std::vector<uint32_t>> &engines, Call call) {
+    Multi &M = *ctx->multi;
+    const size_t G = M.kids.size();
+    std::vector<int> rcs(G, PCU_OK);
+    for (size_t g = 0; g < G; ++g) {
+        pcu_ctx *kid = M.kids[g];
+        kid->hint = pcu_ctx::ShardHint{};
+        if (!plan[g].count) continue;
+        kid->hint.active = chunk != 0;
+        kid->hint.chunk = chunk;
+        kid->hint.first_stream = plan[g].first_stream;
+        kid->hint.last = plan[g].last;
+        kid->hint.keep_dev_sums = out->sums != nullptr;
+        kid->hint.no_sync = true;
+        M.workers[g]->start([&, g, kid] { rcs[g] = call(kid, g); });
+    }
+    for (size_t g = 0; g < G; ++g)
+        if (plan[g].count) M.workers[g]->wait();
+    int rc = PCU_OK;
+    for (size_t g = 0; g < G && !rc; ++g)
+        if (rcs[g]) {
+            rc = rcs[g];
+            ctx->err = "GPU " + std::to_string(M.kids[g]->device) + ": " + M.kids[g]->err;
+        }
+    /* ---- the collective: counters of every shard summed on every GPU */
+    std::vector<size_t> act;
+    for (size_t g = 0; g < G; ++g)
+        if (plan[g].count) act.push_back(g);
+    if (!rc && out->sums && !act.empty()) {
+        /* GPUs without a shard contribute zeros: the communicator spans all of them */
+        for (size_t g = 0; g < G && !rc; ++g)
+            if (!plan[g].count) {
+                pcu_ctx *kid = M.kids[g];
+                if (cudaSetDevice(kid->device) != cudaSuccess || kid->buf[B_SUMS].ensure(64) != cudaSuccess ||
+                    cudaMemsetAsync(kid->buf[B_SUMS].p, 0, 64, kid->stream) != cudaSuccess)
+                    rc = fail(ctx, PCU_ERR_CUDA, "zeroing the counters of an idle GPU failed");
+            }
+        pcu_ctx *k0 = M.kids[0];
+        if (!rc && M.same_device) {
+            SumPtrs S;
+            S.n = (int)G;
+            for (size_t g = 0; g < G; ++g) S.p[g] = reinterpret_cast<const unsigned long long *>(M.kids[g]->buf[B_SUMS].p);
+            cudaSetDevice(k0->device);
+            for (size_t g = 1; g < G; ++g) {
+                cudaEventRecord(M.ev_done[g], M.kids[g]->stream);
+                cudaStreamWaitEvent(k0->stream, M.ev_done[g], 0);
+            }
+            k_sum_shards<<<1, 32, 0, k0->stream>>>(S, reinterpret_cast<unsigned long long *>(k0->buf[B_SUMS].p));
+            k0->launches++;
+            if (cudaGetLastError() != cudaSuccess) rc = fail(ctx, PCU_ERR_CUDA, "k_sum_shards launch failed");
+        } else if (!rc) {
+            ncclResult_t nr = M.nccl.GroupStart();
+            for (size_t g = 0; g < G && nr == ncclSuccess; ++g) {
+                void *buf = M.kids[g]->buf[B_SUMS].p;
+                nr = M.nccl.AllReduce(buf, buf, 8, ncclUint64, ncclSum, M.comms[g], M.kids[g]->stream);
+            }
+            const ncclResult_t ne = M.nccl.GroupEnd();
+            if (nr == ncclSuccess) nr = ne;
+            if (nr != ncclSuccess) rc = fail(ctx, PCU_ERR_CUDA, "ncclAllReduce failed: %s", M.nccl.GetErrorString(nr));
+            M.nccl_calls++;
+        }
+        if (!rc) {
+            cudaSetDevice(k0->device);
+            if (cudaMemcpyAsync(M.pin_sums, k0->buf[B_SUMS].p, 64, cudaMemcpyDeviceToHost, k0->stream) != cudaSuccess)
+                rc = fail(ctx, PCU_ERR_CUDA, "copying the reduced counters failed");
+        }
+    }
+    /* ---- every shard's outputs are complete once its stream drains */
+    for (size_t g = 0; g < G; ++g) {
+        pcu_ctx *kid = M.kids[g];
+        cudaSetDevice(kid->device);
+        const cudaError_t e = cudaStreamSynchronize(kid->stream);
+        if (e != cudaSuccess && !rc) rc = fail(ctx, PCU_ERR_CUDA, "GPU %d: %s", kid->device, cudaGetErrorString(e));
+    }
+    if (!rc) {
+        if (out->sums) {
+            if (act.empty())
+                memset(out->sums, 0, 64);
+            else
+                memcpy(out->sums, M.pin_sums, 64);
+        }
+        if (rng->mode == PCU_MODEL_STREAM)
+            for (size_t g = G; g-- > 0;)
+                if (plan[g].count) { /* the shard that owns the end of the batch holds the post-batch window */
+                    if (M.kids[g]->engine_pending) engine_from_window(M.kids[g]->pin_small, rng->mt_x, rng->mt_p);
+                    break;
+                }
+    }
+    for (pcu_ctx *kid : M.kids) {
+        kid->engine_pending = false;
+        kid->hint = pcu_ctx::ShardHint{};
+    }
+    (void)engines;
+    ctx->path = M.kids[act.empty() ? 0 : act[0]]->path + " x" + std::to_string(act.size()) + "gpu";
+    return rc;
+}
+
+/* Engine of a ragged-depth shard: the caller's, advanced by the draws of the rollouts before it. */
+int shard_engine(const pcu_model_rng *rng, uint64_t words_before, std::vector<uint32_t> &e) {
+    e.resize(MT_N + 1);
+    memcpy(e.data(), rng->mt_x, sizeof(uint32_t) * MT_N);
+    e[MT_N] = *rng->mt_p;
+    return pcu_mt_discard(e.data(), e.data() + MT_N, words_before);
+}
+
+int multi_rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
+    Multi &M = *ctx->multi;
+    int rc = check_common(ctx, b, rng, out);
+    if (rc) return rc;
+    ctx->err.clear();
+    if (M.kids.size() == 1 || b->mem != PCU_MEM_HOST || out->mem != PCU_MEM_HOST || b->n < M.min_rollouts) {
+        /* small batches, and batches that already live on one GPU, stay on the first one */
+        rc = rollout_tree(M.kids[0], b, rng, out);
+        ctx->err = M.kids[0]->err;
+        ctx->path = M.kids[0]->path;
+        return rc;
+    }
+    if (!b->depth && b->depth_u == 0)
+        return fail(ctx, PCU_ERR_INVALID, "depth_bound 0 never terminates in the reference (random-tree.hh:95-99)");
+    std::vector<ShardPlan> plan;
+    uint64_t chunk = 0;
+    plan_shards(M, b->n, rng->mode, b->depth, b->depth_u, &chunk, plan);
+    std::vector<std::vector<uint32_t>> engines(M.kids.size());
+    return multi_dispatch(ctx, plan, chunk, rng, out, engines, [&](pcu_ctx *kid, size_t g) -> int {
+        const ShardPlan &sp = plan[g];
+        pcu_rt_batch sb = *b;
+        sb.n = sp.count;
+        sb.state_seed = off(b->state_seed, sp.first);
+        sb.state_pos = off(b->state_pos, sp.first);
+        sb.transition_seed = off(b->transition_seed, sp.first);
+        sb.depth = off(b->depth, sp.first);
+        sb.payoff_bias = off(b->payoff_bias, sp.first);
+        pcu_model_rng sr = *rng;
+        sr.seeds = off(rng->seeds, sp.first);
+        if (rng->mode == PCU_MODEL_STREAM && !chunk) {
+            const int e = shard_engine(rng, sp.words_before, engines[g]);
+            if (e) return e;
+            sr.mt_x = engines[g].data();
+            sr.mt_p = engines[g].data() + MT_N;
+        }
+        pcu_out so = *out;
+        so.payoff_x2 = off(out->payoff_x2, sp.first);
+        so.payoff_packed2 = off(out->payoff_packed2, sp.first / 4);
+        so.traj = off(out->traj, sp.first * (uint64_t)out->traj_stride * 3);
+        so.traj_hash = off(out->traj_hash, sp.first);
+        so.sums = nullptr;
+        return rollout_tree(kid, &sb, &sr, &so);
+    });
+}
+
+int multi_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_out *out) {
+    Multi &M = *ctx->multi;
+    int rc = check_common(ctx, b, rng, out);
+    if (rc) return rc;
+    ctx->err.clear();
+    if (M.kids.size() == 1 || b->mem != PCU_MEM_HOST || out->mem != PCU_MEM_HOST || b->n < M.min_rollouts ||
+        (!b->depth && b->depth_u == 0)) {
+        rc = rollout_mold(M.kids[0], b, rng, out);
+        ctx->err = M.kids[0]->err;
+        ctx->path = M.kids[0]->path;
+        return rc;
+    }
+    std::vector<ShardPlan> plan;
+    uint64_t chunk = 0;
+    plan_shards(M, b->n, rng->mode, b->depth, b->depth_u, &chunk, plan);
+    std::vector<std::vector<uint32_t>> engines(M.kids.size());
+    return multi_dispatch(ctx, plan, chunk, rng, out, engines, [&](pcu_ctx *kid, size_t g) -> int {
+        const ShardPlan &sp = plan[g];
+        pcu_mold_batch sb = *b;
+        sb.n = sp.count;
+        sb.depth = off(b->depth, sp.first);
+        pcu_model_rng sr = *rng;
+        sr.seeds = off(rng->seeds, sp.first);
+        if (rng->mode == PCU_MODEL_STREAM && !chunk) {
+            const int e = shard_engine(rng, sp.words_before, engines[g]);
+            if (e) return e;
+            sr.mt_x = engines[g].data();
+            sr.mt_p = engines[g].data() + MT_N;
+        }
+        pcu_out so = *out;
+        so.payoff_x2 = off(out->payoff_x2, sp.first);
+        so.payoff_packed2 = off(out->payoff_packed2, sp.first / 4);
+        so.traj = off(out->traj, sp.first * (uint64_t)out->traj_stride * 3);
+        so.traj_hash = off(out->traj_hash, sp.first);
+        so.sums = nullptr;
+        return rollout_mold(kid, &sb, &sr, &so);
+    });
+}
+
+}  // namespace
+
+extern "C" {
+
+int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
+    if (!ctx) return PCU_ERR_INVALID;
+    return ctx->multi ? multi_rollout_tree(ctx, b, rng, out) : rollout_tree(ctx, b, rng, out);
+}
+
+int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_out *out) {
+    if (!ctx) return PCU_ERR_INVALID;
+    return ctx->multi ? multi_rollout_mold(ctx, b, rng, out) : rollout_mold(ctx, b, rng, out);
+}
+
+int pcu_create_multi(const int *device_ids, int n, pcu_ctx **out) {
+    if (!out) return PCU_ERR_INVALID;
+    *out = nullptr;
+    if (!device_ids || n < 1 || n > 16) return PCU_ERR_INVALID;
+    bool all_same = true, all_distinct = true;
+    for (int i = 0; i < n; ++i)
+        for (int j = 0; j < i; ++j) {
+            if (device_ids[i] == device_ids[j]) all_distinct = false;
+            else all_same = false;
+        }
+    if (n > 1 && !all_same && !all_distinct) return PCU_ERR_INVALID; /* a communicator cannot hold a GPU twice */
+    pcu_ctx *ctx = new pcu_ctx();
+    Multi *M = new Multi();
+    ctx->multi = M;
+    ctx->device = device_ids[0];
+    M->same_device = n > 1 && all_same;
+    auto bail = [&](int code) {
+        pcu_destroy(ctx);
+        return code;
+    };
+    for (int i = 0; i < n; ++i) {
+        pcu_ctx *kid = nullptr;
+        const int rc = pcu_create(device_ids[i], &kid);
+        if (rc) return bail(rc);
+        M->kids.push_back(kid);
+        M->workers.emplace_back(new Worker());
+    }
+    ctx->sms = M->kids[0]->sms;
+    M->min_rollouts = (uint64_t)n << 16;
+    cudaSetDevice(device_ids[0]);
+    if (cudaHostAlloc(reinterpret_cast<void **>(&M->pin_sums), 64, cudaHostAllocPortable) != cudaSuccess) return bail(PCU_ERR_CUDA);
+    if (M->same_device) {
+        M->ev_done.resize(n);
+        for (int i = 0; i < n; ++i)
+            if (cudaEventCreateWithFlags(&M->ev_done[i], cudaEventDisableTiming) != cudaSuccess) return bail(PCU_ERR_CUDA);
+    } else if (n > 1) {
+        /* one process, one communicator per GPU; there is no non-NCCL path between distinct GPUs */
+        if (!M->nccl.load()) return bail(PCU_ERR_UNSUPPORTED);
+        M->comms.assign(n, nullptr);
+        if (M->nccl.CommInitAll(M->comms.data(), n, device_ids) != ncclSuccess) {
+            M->comms.clear();
+            return bail(PCU_ERR_CUDA);
+        }
+    }
+    *out = ctx;
+    return PCU_OK;
+}
+
+int pcu_device_count(const pcu_ctx *ctx) { return !ctx ? 0 : ctx->multi ? (int)ctx->multi->kids.size() : 1; }
+
+int pcu_get_stat(pcu_ctx *ctx, const char *key, double *value) {
+    if (!ctx || !key || !value) return PCU_ERR_INVALID;
+    const pcu_ctx *c = ctx->multi ? ctx->multi->kids[0] : ctx;
+    if (!strcmp(key, "last_chunk")) *value = (double)c->last_chunk;
+    else if (!strcmp(key, "last_streams")) *value = (double)c->last_streams;
+    else if (!strcmp(key, "last_family_build_ms")) {
+        *value = 0;
+        if (ctx->multi) { for (const pcu_ctx *k : ctx->multi->kids) *value = std::max(*value, k->last_family_ms); }
+        else *value = c->last_family_ms;
+    } else if (!strcmp(key, "last_table_build_ms")) *value = c->last_table_ms;
+    else if (!strcmp(key, "nccl_calls")) *value = ctx->multi ? (double)ctx->multi->nccl_calls : 0.0;
+    else return fail(ctx, PCU_ERR_INVALID, "unknown statistic %s", key);
+    return PCU_OK;
+}
+
+/* Build (and upload) now what the first call of a new batch shape would otherwise build inside the call: the family of
+ * jump polynomials for `n` uniform-depth rollouts in mode S (~80 ms of host GF(2) arithmetic per new stride). */
+int pcu_warmup(pcu_ctx *ctx, uint64_t n, uint32_t depth) {
+    if (!ctx || depth == 0) return PCU_ERR_INVALID;
+    std::string jerr;
+    if (ctx->multi) {
+        Multi &M = *ctx->multi;
+        if (M.kids.size() == 1 || n < M.min_rollouts) return pcu_warmup(M.kids[0], n, depth);
+        std::vector<ShardPlan> plan;
+        uint64_t chunk = 0;
+        plan_shards(M, n, PCU_MODEL_STREAM, nullptr, depth, &chunk, plan);
+        for (size_t g = 0; g < M.kids.size(); ++g) {
+            if (!plan[g].count) continue;
+            pcu_ctx *kid = M.kids[g];
+            cudaSetDevice(kid->device);
+            const uint64_t streams = (plan[g].count + chunk - 1) / chunk;
+            if (kid->jump.prepare(kid->stream, plan[g].first_stream, streams, 4ull * depth * chunk, &jerr))
+                return fail(ctx, PCU_ERR_CUDA, "warm-up failed: %s", jerr.c_str());
+        }
+        return PCU_OK;
+    }
+    CU(cudaSetDevice(ctx->device));
+    const uint64_t chunk = pick_rollout_chunk(n, (uint64_t)ctx->sms * streams_per_sm_for(ctx, n, depth), 128);
+    if (ctx->jump.prepare(ctx->stream, 0, (n + chunk - 1) / chunk, 4ull * depth * chunk, &jerr))
+        return fail(ctx, PCU_ERR_CUDA, "warm-up failed: %s", jerr.c_str());
+    return PCU_OK;
 }
 
 int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_second) {
     if (!ctx || !ops_per_second) return PCU_ERR_INVALID;
+    if (ctx->multi) return pcu_measure_int_peak(ctx->multi->kids[0], variant, reps, ops_per_second);
     CU(cudaSetDevice(ctx->device));
     const int iters = 4096;
     const int blocks = ctx->sms * 8, threads = 256;

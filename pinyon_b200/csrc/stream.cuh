@@ -186,6 +186,8 @@ struct Stream2Params {
     const int32_t *bias;
     int32_t bias_u;
     uint8_t *payoff;
+    uint8_t *payoff_packed2; /* optional 2-bit payoffs, four rollouts per byte (rb = 128 only) */
+    uint32_t vec_ok;         /* chunk % 4 == 0 and payoff / traj_hash suitably aligned: vector stores allowed */
     uint8_t *traj;
     uint32_t traj_stride;
     uint32_t *traj_hash;
@@ -231,8 +233,9 @@ struct QueueSink {
  * Codes of a rollout are contiguous in the ring (index & qmask).  All return the trajectory
  * hash; TRAJ also writes (row, col, chance) bytes. */
 template <bool TRAJ>
-__device__ __forceinline__ void put_traj(uint8_t *tr, uint32_t s, uint32_t code, uint32_t cols, uint32_t ch) {
-    if (TRAJ) {
+__device__ __forceinline__ void put_traj(uint8_t *tr, uint32_t s, uint32_t code, uint32_t cols, uint32_t ch,
+                                         uint32_t stride) {
+    if (TRAJ && s < stride) { /* steps past traj_stride are played and hashed, not recorded (as the oracle) */
         const uint32_t rr = code / cols;
         tr[3 * s + 0] = (uint8_t)rr;
         tr[3 * s + 1] = (uint8_t)(code - rr * cols);
@@ -242,13 +245,13 @@ __device__ __forceinline__ void put_traj(uint8_t *tr, uint32_t s, uint32_t code,
 
 template <bool TRAJ, typename CodeT>
 __device__ __forceinline__ uint32_t walk_mold(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
-                                              uint8_t *tr) {
+                                              uint8_t *tr, uint32_t tstride) {
     uint32_t h = PCU_HASH_INIT;
 #pragma unroll 5
     for (uint32_t s = 0; s < d; ++s) {
         const uint32_t code = queue[(qb + s) & qmask];
         h = hash_step(h, code, 0);
-        put_traj<TRAJ>(tr, s, code, cols, 0);
+        put_traj<TRAJ>(tr, s, code, cols, 0, tstride);
     }
     return h;
 }
@@ -257,7 +260,8 @@ __device__ __forceinline__ uint32_t walk_mold(const CodeT *queue, uint32_t qmask
  * a step is discard(row * cols + col), one bias draw, then 2 * rows * cols strategy draws. */
 template <bool TRAJ, typename CodeT>
 __device__ __forceinline__ uint32_t walk_tree1(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
-                                               const int8_t *tb, uint32_t p, uint32_t adv, int &bias, uint8_t *tr) {
+                                               const int8_t *tb, uint32_t p, uint32_t adv, int &bias, uint8_t *tr,
+                                               uint32_t tstride) {
     uint32_t h = PCU_HASH_INIT;
     int b = bias;
 #pragma unroll 5
@@ -267,7 +271,7 @@ __device__ __forceinline__ uint32_t walk_tree1(const CodeT *queue, uint32_t qmas
         b += tb[t];
         p = t + adv;
         h = hash_step(h, code, 0);
-        put_traj<TRAJ>(tr, s, code, cols, 0);
+        put_traj<TRAJ>(tr, s, code, cols, 0, tstride);
     }
     bias = b;
     return h;
@@ -277,7 +281,7 @@ __device__ __forceinline__ uint32_t walk_tree1(const CodeT *queue, uint32_t qmas
 template <bool TRAJ, typename CodeT>
 __device__ __forceinline__ uint32_t walk_treeT(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
                                                uint32_t T, const int8_t *tb, const uint8_t *tch, uint32_t p,
-                                               uint32_t gen_words, int &bias, uint8_t *tr) {
+                                               uint32_t gen_words, int &bias, uint8_t *tr, uint32_t tstride) {
     uint32_t h = PCU_HASH_INIT;
     int b = bias;
     uint32_t gb = p - gen_words; /* where the current chance strategies were drawn */
@@ -290,10 +294,177 @@ __device__ __forceinline__ uint32_t walk_treeT(const CodeT *queue, uint32_t qmas
         b += tb[t];
         gb = t + 2;
         h = hash_step(h, code, ch);
-        put_traj<TRAJ>(tr, s, code, cols, ch);
+        put_traj<TRAJ>(tr, s, code, cols, ch, tstride);
     }
     bias = b;
     return h;
+}
+
+/* One batch of rb = 32 Q rollouts whose codes are complete.  Lane l plays the Q CONSECUTIVE rollouts
+ * Q l .. Q l + Q - 1 of the batch, their table walks interleaved (Q independent chains of dependent
+ * shared-memory loads), and stores their outputs as ONE vector: Q payoff bytes (Q = 4: a warp writes one
+ * contiguous 128-byte line, which is also one PCIe write when the payoffs go straight to pinned host memory),
+ * or one byte of 2-bit payoffs (Q = 4, pcu_out.payoff_packed2), and Q trajectory hashes.  Lanes past the end of
+ * a partial batch replay their last live rollout and store nothing for it. */
+template <int KIND, typename CodeT, int Q>
+__device__ __forceinline__ void consume_batch(const Stream2Params &P, const CodeT *queue, uint32_t qmask, const uint8_t *tab,
+                                              uint64_t i0, uint32_t kbase, uint32_t live, int lane, RolloutAcc &acc) {
+    const uint32_t d = P.depth, T = P.T;
+    const uint32_t rl = (uint32_t)Q * lane;
+    if (rl >= live) return;
+    const uint32_t mine = (live - rl < (uint32_t)Q) ? live - rl : (uint32_t)Q; /* 1..Q rollouts of this lane */
+    const uint64_t il = i0 + rl;
+    uint32_t h[Q], pay[Q];
+    if (P.traj) { /* trajectories: one rollout at a time (tests and small batches) */
+#pragma unroll
+        for (int j = 0; j < Q; ++j) {
+            h[j] = PCU_HASH_INIT;
+            pay[j] = 0;
+            if ((uint32_t)j >= mine) continue;
+            const uint64_t i = il + j;
+            const uint32_t qb = kbase + (rl + j) * d;
+            uint8_t *tr = P.traj + (size_t)i * P.traj_stride * 3;
+            if (KIND == KIND_MOLD) {
+                h[j] = walk_mold<true>(queue, qmask, qb, d, P.cols, tr, P.traj_stride);
+            } else {
+                const uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
+                int bias = P.bias ? P.bias[i] : P.bias_u;
+                const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
+                if (T == 1)
+                    h[j] = walk_tree1<true>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr, P.traj_stride);
+                else
+                    h[j] = walk_treeT<true>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr,
+                                            P.traj_stride);
+                pay[j] = (uint32_t)((bias > 0) - (bias < 0) + 1);
+            }
+            for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
+        }
+    } else {
+        uint32_t qb[Q], p[Q];
+        int bias[Q];
+#pragma unroll
+        for (int j = 0; j < Q; ++j) {
+            const uint32_t jj = ((uint32_t)j < mine) ? (uint32_t)j : mine - 1;
+            h[j] = PCU_HASH_INIT;
+            pay[j] = 0;
+            qb[j] = kbase + (rl + jj) * d;
+            if (KIND == KIND_TREE) {
+                p[j] = (P.state_pos ? P.state_pos[il + jj] : P.state_pos_u) - P.tab_base;
+                bias[j] = P.bias ? P.bias[il + jj] : P.bias_u;
+            }
+        }
+        if (KIND == KIND_MOLD) {
+#pragma unroll 2
+            for (uint32_t s = 0; s < d; ++s) {
+#pragma unroll
+                for (int j = 0; j < Q; ++j) h[j] = hash_step(h[j], queue[(qb[j] + s) & qmask], 0);
+            }
+        } else if (T == 1) {
+            /* chance strategies are all 1, chance action 0 (random-tree.hh:115-135 with p - 1 <= 0): a step is
+             * discard(row * cols + col), one bias draw, then 2 * rows * cols strategy draws */
+            const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
+            const uint32_t adv = 2 + P.gen_words;
+#pragma unroll 2
+            for (uint32_t s = 0; s < d; ++s) {
+#pragma unroll
+                for (int j = 0; j < Q; ++j) {
+                    const uint32_t code = queue[(qb[j] + s) & qmask];
+                    const uint32_t t = p[j] + code; /* discard(row*cols + col): random-tree.hh:88-89 */
+                    bias[j] += tb[t];
+                    p[j] = t + adv;
+                    h[j] = hash_step(h[j], code, 0);
+                }
+            }
+        } else {
+            const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
+            const uint8_t *tch = tab + P.tab_len;
+            const uint32_t gen = P.gen_words;
+#pragma unroll
+            for (int j = 0; j < Q; ++j) p[j] -= gen; /* where the current chance strategies were drawn */
+#pragma unroll 2
+            for (uint32_t s = 0; s < d; ++s) {
+#pragma unroll
+                for (int j = 0; j < Q; ++j) {
+                    const uint32_t code = queue[(qb[j] + s) & qmask];
+                    const uint32_t st = code * T;
+                    const uint32_t ch = tch[p[j] + 2 * st];
+                    const uint32_t t = p[j] + gen + st + ch; /* discard(get_transition_idx): random-tree.hh:88-89,149-152 */
+                    bias[j] += tb[t];
+                    p[j] = t + 2;
+                    h[j] = hash_step(h[j], code, ch);
+                }
+            }
+        }
+        if (KIND == KIND_TREE) {
+#pragma unroll
+            for (int j = 0; j < Q; ++j) pay[j] = (uint32_t)((bias[j] > 0) - (bias[j] < 0) + 1);
+        }
+    }
+    /* ---- outputs and counters */
+    uint32_t packed = 0, bytes = 0;
+#pragma unroll
+    for (int j = 0; j < Q; ++j) {
+        if ((uint32_t)j < mine) {
+            bytes |= pay[j] << (8 * j);
+            packed |= pay[j] << (2 * j);
+            if (KIND == KIND_MOLD) {
+                acc.d += 1;
+            } else {
+                acc.w += (pay[j] == 2);
+                acc.d += (pay[j] == 1);
+                acc.l += (pay[j] == 0);
+            }
+            acc.h += h[j];
+            acc.n += 1;
+        }
+    }
+    if (P.payoff) {
+        if (Q == 4 && P.vec_ok && mine == 4) {
+            *reinterpret_cast<uint32_t *>(P.payoff + il) = bytes;
+        } else if (Q == 2 && P.vec_ok && mine == 2) {
+            *reinterpret_cast<uint16_t *>(P.payoff + il) = (uint16_t)bytes;
+        } else {
+#pragma unroll
+            for (int j = 0; j < Q; ++j)
+                if ((uint32_t)j < mine) P.payoff[il + j] = (uint8_t)pay[j];
+        }
+    }
+    if (Q == 4 && P.payoff_packed2) P.payoff_packed2[il >> 2] = (uint8_t)packed; /* il is a multiple of 4 (host-checked) */
+    if (P.traj_hash) {
+        if (Q == 4 && P.vec_ok && mine == 4) {
+            *reinterpret_cast<uint4 *>(P.traj_hash + il) = make_uint4(h[0], h[1], h[2], h[3]);
+        } else {
+#pragma unroll
+            for (int j = 0; j < Q; ++j)
+                if ((uint32_t)j < mine) P.traj_hash[il + j] = h[j];
+        }
+    }
+}
+
+/* The consumer warp of one stream: waits for each pass of its generator and plays every batch the pass completed. */
+template <int KIND, typename CodeT, int Q>
+__device__ __forceinline__ void consume_stream(const Stream2Params &P, const CodeT *queue, uint32_t qmask, const uint8_t *tab,
+                                               int bar, uint64_t first, uint64_t cnt, int lane, RolloutAcc &acc) {
+    constexpr uint32_t RB = 32u * Q;
+    const uint32_t d = P.depth;
+    const uint64_t total_steps = cnt * d;
+    const uint64_t nbuf = (cnt + RB - 1) / RB;
+    const uint64_t npass = (total_steps + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
+    uint64_t k = 0; /* next batch of RB rollouts */
+    for (uint64_t j = 0; j < npass; ++j) {
+        nb_sync(bar + (int)(j & 1));
+        const uint64_t avail = ((j + 1) * GW_PASS_STEPS < total_steps) ? (j + 1) * GW_PASS_STEPS : total_steps;
+        for (; k < nbuf; ++k) { /* every batch whose codes pass j completed */
+            const uint64_t r0 = k * RB;
+            const uint32_t live = (uint32_t)((cnt - r0 < RB) ? cnt - r0 : RB);
+            if ((r0 + live) * d > avail) break;
+            consume_batch<KIND, CodeT, Q>(P, queue, qmask, tab, first + r0, (uint32_t)((r0 * d) & qmask), live, lane, acc);
+        }
+        if (j + 2 < npass) {
+            __syncwarp();
+            nb_arrive(bar + 2 + (int)(j & 1));
+        }
+    }
 }
 
 template <int KIND, typename CodeT, bool TAB_SMEM>
@@ -301,7 +472,6 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t d = P.depth;
-    const uint32_t B = P.rb * d; /* codes per queue buffer */
     /* layout: rings [PAIRS][896] u32 | queues [PAIRS][Q + 16] CodeT | tables */
     uint32_t *rings = reinterpret_cast<uint32_t *>(smem_raw);
     CodeT *queues = reinterpret_cast<CodeT *>(rings + GW_PAIRS * GW_RING);
@@ -347,272 +517,12 @@ __global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P
 
     /* ---- consumer warp */
     RolloutAcc acc;
-    const uint64_t nbuf = (cnt + P.rb - 1) / P.rb;
-    const uint32_t T = P.T;
-    const uint64_t npass = (total_steps + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
-    uint64_t k = 0; /* next batch of rb rollouts */
-    for (uint64_t j = 0; j < npass; ++j) {
-      nb_sync(bar + (int)(j & 1));
-      const uint64_t avail = ((j + 1) * GW_PASS_STEPS < total_steps) ? (j + 1) * GW_PASS_STEPS : total_steps;
-      for (; k < nbuf; ++k) { /* every batch whose codes pass j completed */
-        const uint64_t r0 = k * P.rb;
-        const uint32_t live = (uint32_t)((cnt - r0 < P.rb) ? cnt - r0 : P.rb);
-        if ((r0 + live) * d > avail) break;
-        const uint32_t kbase = (uint32_t)((r0 * d) & qmask);
-        for (uint32_t r = lane; r < live; r += 32) {
-            const uint64_t i = first + r0 + r;
-            const uint32_t qb = kbase + r * d;
-            uint32_t h = PCU_HASH_INIT, pay = 0;
-            uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
-            if (KIND == KIND_MOLD) {
-                if (tr)
-                    h = walk_mold<true>(queue, qmask, qb, d, P.cols, tr);
-                else
-                    h = walk_mold<false>(queue, qmask, qb, d, P.cols, tr);
-                acc.d += 1;
-            } else {
-                const uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
-                int bias = P.bias ? P.bias[i] : P.bias_u;
-                const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
-                if (T == 1) {
-                    if (tr)
-                        h = walk_tree1<true>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr);
-                    else
-                        h = walk_tree1<false>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr);
-                } else {
-                    if (tr)
-                        h = walk_treeT<true>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr);
-                    else
-                        h = walk_treeT<false>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr);
-                }
-                pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
-                acc.w += (pay == 2);
-                acc.d += (pay == 1);
-                acc.l += (pay == 0);
-            }
-            if (tr)
-                for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
-            if (P.payoff) P.payoff[i] = (uint8_t)pay;
-            if (P.traj_hash) P.traj_hash[i] = h;
-            acc.h += h;
-            acc.n += 1;
-        }
-      }
-      if (j + 2 < npass) {
-          __syncwarp();
-          nb_arrive(bar + 2 + (int)(j & 1));
-      }
-    }
-    if (P.sums) {
-        acc.w = warp_sum_u64(acc.w);
-        acc.d = warp_sum_u64(acc.d);
-        acc.l = warp_sum_u64(acc.l);
-        acc.h = warp_sum_u64(acc.h);
-        acc.n = warp_sum_u64(acc.n);
-        if (lane == 0) {
-            if (acc.w) atomicAdd(P.sums + 0, acc.w);
-            if (acc.d) atomicAdd(P.sums + 1, acc.d);
-            if (acc.l) atomicAdd(P.sums + 2, acc.l);
-            atomicAdd(P.sums + 3, acc.n * d);
-            atomicAdd(P.sums + 4, acc.h);
-        }
-    }
-}
-
-/* ------------------------------------------------------------------ k_stream3 */
-/* One CTA = one model stream = FIVE warps, so that the serial part of the generator (the recurrence) is
- * no longer in the same in-order instruction stream as the embarrassingly parallel part (temper, reduce):
- *   G   (warp 0)  the recurrence only: loads, twist, ring store, and a copy of the raw words into a
- *                 double-buffered raw queue, one 896-word pass at a time
- *   T0  (warp 1)  tempers and reduces the FIRST step of every lane (x0) to action codes
- *   T1  (warp 2)  the same for the SECOND step of every lane (x1)
- *   W0, W1 (warps 3, 4)  play the rollouts a pass completed against the state-stream table, alternate batches
- * Eight mbarriers (two per edge, by parity of the pass): RAWFULL G -> T0,T1; RAWEMPTY T0,T1 -> G; CODES T0,T1 -> W0,W1;
- * QEMPTY W0,W1 -> T0,T1.  r1c ncu of k_stream2: one generator warp per scheduler issues at 2.4 cycles per instruction
- * (fixed-latency waits with nothing else to issue); the ALU pipe was 62 % busy. */
-constexpr int S3_THREADS = 160;
-constexpr int S3_RAWQ_U4 = 2 * 4 * 2 * 32; /* [parity][group][half][lane] uint4 */
-
-/* Shared-memory mbarriers instead of named barriers: the 16 hardware barriers are an SM-wide pool, and a CTA that
- * addresses them by register reserves all 16 -> one CTA per SM (first k_stream3 build: 1.68 ms instead of 1.11).
- * One elected lane arrives (release) after __syncwarp; waiters spin on try_wait (acquire), which suspends in
- * hardware for a bounded time rather than burning issue slots. */
-__device__ __forceinline__ void mb_init(uint64_t *bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mb_arrive(uint64_t *bar, int lane) {
-    __syncwarp();
-    if (lane == 0)
-        asm volatile("mbarrier.arrive.release.cta.shared::cta.b64 _, [%0];" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
-}
-__device__ __forceinline__ void mb_wait(uint64_t *bar, uint32_t parity) {
-    const uint32_t a = (uint32_t)__cvta_generic_to_shared(bar);
-    uint32_t done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.acquire.cta.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done)
-            : "r"(a), "r"(parity)
-            : "memory");
-    } while (!done);
-}
-
-template <int PH>
-__device__ __forceinline__ void s3_group(uint32_t *ring, int l4, bool active, uint4 *rq, int lane) {
-    GwOps o;
-    gw_load<PH>(ring, l4, o);
-    const uint4 x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);
-    const uint4 x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);
-    gw_store<PH>(ring, l4, active, x0, x1);
-    rq[(PH * 2 + 0) * 32 + lane] = x0;
-    rq[(PH * 2 + 1) * 32 + lane] = x1;
-    __syncwarp();
-}
-
-template <int KIND, typename CodeT, bool TAB_SMEM>
-__global__ void __launch_bounds__(S3_THREADS) k_stream3(const Stream2Params P) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t d = P.depth;
-    /* layout: mbarriers [8] u64 | ring [896] u32 | raw queue [512] uint4 | code queue [Q + 16] CodeT | tables */
-    uint64_t *mbar = reinterpret_cast<uint64_t *>(smem_raw);
-    uint32_t *ring = reinterpret_cast<uint32_t *>(smem_raw + 64);
-    uint4 *rawq = reinterpret_cast<uint4 *>(ring + GW_RING);
-    CodeT *queue = reinterpret_cast<CodeT *>(rawq + S3_RAWQ_U4);
-    const uint32_t Q = P.qlen;
-    const uint8_t *tab = P.tab;
-    if (KIND == KIND_TREE && TAB_SMEM) {
-        uint8_t *stab = reinterpret_cast<uint8_t *>(queue + (size_t)(Q + 16));
-        stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
-        const uint32_t bytes = P.tab_len * (P.T > 1 ? 2u : 1u);
-        for (uint32_t i = tid; i < bytes; i += blockDim.x) stab[i] = P.tab[i];
-        tab = stab;
-    }
-    const uint32_t stream = blockIdx.x;
-    if (warp == 0) gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
-    enum { RAWFULL = 0, RAWEMPTY = 2, CODES = 4, QEMPTY = 6 };
-    if (tid < 8) mb_init(mbar + tid, tid >= RAWEMPTY ? 2u : 1u); /* all but RAWFULL: two warps arrive */
-    __syncthreads();
-
-    const uint64_t first = (uint64_t)stream * P.chunk;
-    const uint64_t cnt = (first + P.chunk <= P.n) ? P.chunk : P.n - first;
-    const uint64_t total_steps = cnt * d;
-    const uint32_t qmask = Q - 1;
-    const uint64_t groups = (total_steps + GW_STEPS - 1) / GW_STEPS;
-    const uint64_t npass = (groups + 3) / 4;
-    const bool active = lane < GW_ACTIVE;
-
-    if (warp == 0) { /* ---- G: the recurrence */
-        const int l4 = 4 * (active ? lane : GW_ACTIVE - 1);
-        for (uint64_t j = 0; j < npass; ++j) {
-            const int par = (int)(j & 1);
-            if (j >= 2) mb_wait(mbar + RAWEMPTY + par, (uint32_t)(((j >> 1) - 1) & 1));
-            uint4 *rq = rawq + par * (S3_RAWQ_U4 / 2);
-            const uint64_t g = 4 * j;
-            s3_group<0>(ring, l4, active, rq, lane);
-            if (g + 1 < groups) s3_group<1>(ring, l4, active, rq, lane);
-            if (g + 2 < groups) s3_group<2>(ring, l4, active, rq, lane);
-            if (g + 3 < groups) s3_group<3>(ring, l4, active, rq, lane);
-            mb_arrive(mbar + RAWFULL + par, lane);
-        }
-        if (stream + 1 == P.streams && P.end_window) {
-            const uint64_t words = 4 * total_steps;
-            uint32_t w_end = (uint32_t)(words % GW_RING);
-            if (w_end == 0 && words > 0) w_end = GW_RING;
-            gw_dump_window(ring, w_end, P.end_window, lane);
-        }
-        return;
-    }
-
-    /* ---- T0 / T1 (warps 1, 2): temper + reduce one step per lane and group */
-    if (warp < 3) {
-        const int half = warp - 1;
-        uint32_t qpos = 0;
-        for (uint64_t j = 0; j < npass; ++j) {
-            const int par = (int)(j & 1);
-            mb_wait(mbar + RAWFULL + par, (uint32_t)((j >> 1) & 1));
-            const uint4 *rq = rawq + par * (S3_RAWQ_U4 / 2);
-            /* all four groups at once: 16 independent temper chains in flight.  Groups past the end of the stream
-             * hold stale words; their codes land beyond the last step anyone reads (two passes of slack). */
-            uint4 xs[4];
-#pragma unroll
-            for (int ph = 0; ph < 4; ++ph) xs[ph] = rq[(ph * 2 + half) * 32 + lane];
-            uint32_t cs[4];
-#pragma unroll
-            for (int ph = 0; ph < 4; ++ph) cs[ph] = gw_code(xs[ph], P.mrow, P.mcol, P.cols);
-            if (j + 2 < npass) mb_arrive(mbar + RAWEMPTY + par, lane);
-            if (j >= 2) mb_wait(mbar + QEMPTY + par, (uint32_t)(((j >> 1) - 1) & 1));
-#pragma unroll
-            for (int ph = 0; ph < 4; ++ph) {
-                const uint32_t idx = active ? ((qpos + ph * GW_STEPS + half * GW_ACTIVE + lane) & qmask) : qmask + 1;
-                queue[idx] = (CodeT)cs[ph];
-            }
-            qpos = (qpos + GW_PASS_STEPS) & qmask;
-            mb_arrive(mbar + CODES + par, lane);
-        }
-        return;
-    }
-
-    /* ---- W0 / W1 (warps 3, 4): play the rollouts each pass completes, alternate batches of rb (a walk is a chain
-     * of dependent shared-memory loads: one walker could not keep up with the split generator) */
-    const int wid = warp - 3;
-    RolloutAcc acc;
-    const uint64_t nbuf = (cnt + P.rb - 1) / P.rb;
-    const uint32_t T = P.T;
-    uint64_t k = 0; /* next batch of rb rollouts */
-    for (uint64_t j = 0; j < npass; ++j) {
-        const int par = (int)(j & 1);
-        mb_wait(mbar + CODES + par, (uint32_t)((j >> 1) & 1));
-        const uint64_t avail = ((j + 1) * GW_PASS_STEPS < total_steps) ? (j + 1) * GW_PASS_STEPS : total_steps;
-        for (; k < nbuf; ++k) { /* every batch whose codes pass j completed */
-            const uint64_t r0 = k * P.rb;
-            const uint32_t live = (uint32_t)((cnt - r0 < P.rb) ? cnt - r0 : P.rb);
-            if ((r0 + live) * d > avail) break;
-            if ((int)(k & 1) != wid) continue;
-            const uint32_t kbase = (uint32_t)((r0 * d) & qmask);
-            for (uint32_t r = lane; r < live; r += 32) {
-                const uint64_t i = first + r0 + r;
-                const uint32_t qb = kbase + r * d;
-                uint32_t h = PCU_HASH_INIT, pay = 0;
-                uint8_t *tr = P.traj ? P.traj + (size_t)i * P.traj_stride * 3 : nullptr;
-                if (KIND == KIND_MOLD) {
-                    if (tr)
-                        h = walk_mold<true>(queue, qmask, qb, d, P.cols, tr);
-                    else
-                        h = walk_mold<false>(queue, qmask, qb, d, P.cols, tr);
-                    acc.d += 1;
-                } else {
-                    const uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
-                    int bias = P.bias ? P.bias[i] : P.bias_u;
-                    const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
-                    if (T == 1) {
-                        if (tr)
-                            h = walk_tree1<true>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr);
-                        else
-                            h = walk_tree1<false>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr);
-                    } else {
-                        if (tr)
-                            h = walk_treeT<true>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr);
-                        else
-                            h = walk_treeT<false>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr);
-                    }
-                    pay = (uint32_t)((bias > 0) - (bias < 0) + 1);
-                    acc.w += (pay == 2);
-                    acc.d += (pay == 1);
-                    acc.l += (pay == 0);
-                }
-                if (tr)
-                    for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
-                if (P.payoff) P.payoff[i] = (uint8_t)pay;
-                if (P.traj_hash) P.traj_hash[i] = h;
-                acc.h += h;
-                acc.n += 1;
-            }
-        }
-        if (j + 2 < npass) mb_arrive(mbar + QEMPTY + par, lane);
-    }
+    if (P.rb == 128)
+        consume_stream<KIND, CodeT, 4>(P, queue, qmask, tab, bar, first, cnt, lane, acc);
+    else if (P.rb == 64)
+        consume_stream<KIND, CodeT, 2>(P, queue, qmask, tab, bar, first, cnt, lane, acc);
+    else
+        consume_stream<KIND, CodeT, 1>(P, queue, qmask, tab, bar, first, cnt, lane, acc);
     if (P.sums) {
         acc.w = warp_sum_u64(acc.w);
         acc.d = warp_sum_u64(acc.d);

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     missing = [s for s in declared if not hasattr(lib, s)]
     assert not missing
     assert sorted(capi.EXPORTS) == declared  # the ctypes binding tracks the header
-    assert lib.pcu_version() == 100
+    assert lib.pcu_version() == 200
 
 
 def test_struct_layouts_match_header():
@@ -43,7 +43,8 @@ def test_struct_layouts_match_header():
       printf("%zu %zu %zu %zu\n", sizeof(pcu_model_rng), sizeof(pcu_rt_batch), sizeof(pcu_mold_batch), sizeof(pcu_out));
       printf("%zu %zu %zu %zu\n", offsetof(pcu_rt_batch, state_pos_u), offsetof(pcu_rt_batch, depth_u),
              offsetof(pcu_rt_batch, rows), offsetof(pcu_rt_batch, thr_q));
-      printf("%zu %zu %zu\n", offsetof(pcu_out, traj_stride), offsetof(pcu_out, sums), offsetof(pcu_mold_batch, n_actions));
+      printf("%zu %zu %zu %zu\n", offsetof(pcu_out, traj_stride), offsetof(pcu_out, sums), offsetof(pcu_mold_batch, n_actions),
+             offsetof(pcu_out, payoff_packed2));
       return 0; }
     """
     with tempfile.TemporaryDirectory() as d:
@@ -55,7 +56,8 @@ def test_struct_layouts_match_header():
     assert vals[:4] == [C.sizeof(capi.ModelRng), C.sizeof(capi.RtBatch), C.sizeof(capi.MoldBatch), C.sizeof(capi.Out)]
     assert vals[4:8] == [capi.RtBatch.state_pos_u.offset, capi.RtBatch.depth_u.offset, capi.RtBatch.rows.offset,
                          capi.RtBatch.thr_q.offset]
-    assert vals[8:] == [capi.Out.traj_stride.offset, capi.Out.sums.offset, capi.MoldBatch.n_actions.offset]
+    assert vals[8:] == [capi.Out.traj_stride.offset, capi.Out.sums.offset, capi.MoldBatch.n_actions.offset,
+                        capi.Out.payoff_packed2.offset]
 
 
 def test_host_engine_matches_oracle(oracle):
@@ -125,6 +127,31 @@ def test_window_reconstruction_every_position(oracle):
         assert [e.next() for _ in range(64)] == exp.tolist(), pre
 
 
+def test_jump_family_slices_are_the_family(oracle):
+    """A multi-GPU shard applies polynomials x^((first + j) * stride): its slice of ONE global family.  The host
+    cache serves any [first, first + count) of a stride and survives eviction of other strides."""
+    lib = capi.load_library()
+    stride = 4 * 10 * 128
+    lib.pcu_set_option  # the byte cap is a context option; exercised on the GPU box
+    for first, c in ((0, 3), (37, 0), (37, 5), (500, 1)):
+        e = Engine(4)
+        e.next()
+        assert lib.pcu_mt_discard_family(e.x.ctypes.data, e.p.ctypes.data, stride, first + c) == 0
+        exp = np.zeros(100, np.uint32)
+        oracle.orc_mt_words(4, 1 + (first + c) * stride, 100, exp.ctypes.data)
+        assert [e.next() for _ in range(100)] == exp.tolist(), (first, c)
+
+
+def test_unpack2_roundtrip():
+    rng = np.random.default_rng(0)
+    for n in (0, 1, 3, 4, 5, 1001):
+        pay = rng.integers(0, 3, n).astype(np.uint8)
+        packed = np.zeros((n + 3) // 4, np.uint8)
+        for i, v in enumerate(pay):
+            packed[i // 4] |= v << (2 * (i % 4))
+        assert np.array_equal(capi.unpack2(packed, n), pay)
+
+
 def test_no_gpu_means_loud_failure():
     """Without an sm_100 device there is no product path: pcu_create fails, nothing computes."""
     try:
@@ -136,6 +163,9 @@ def test_no_gpu_means_loud_failure():
         pass
     with pytest.raises(PcuError) as e:
         capi.Context(0)
+    assert e.value.code == capi.PCU_ERR_CUDA
+    with pytest.raises(PcuError) as e:
+        capi.Context([0, 1])  # the multi-GPU parent fails the same way: no device, no context
     assert e.value.code == capi.PCU_ERR_CUDA
 
 

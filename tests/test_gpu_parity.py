@@ -5,7 +5,8 @@ import numpy as np
 import pytest
 
 from oracle import loader
-from pinyon_b200 import Engine, PcuError
+from pinyon_b200 import Context, Engine, PcuError
+from pinyon_b200.capi import unpack2
 
 pytestmark = pytest.mark.gpu
 
@@ -449,26 +450,330 @@ def test_nine_transitions_are_refused(ctx):
     assert e.value.code == -3
 
 
+# ---------------------------------------------------------------------------------------------
+# Fused-kernel geometry: every streams_per_sm x rb the library can run (the auto setting picks 8 streams per SM from
+# 2.5e8 rollout-steps per call: every BASELINE configs[2..3] headline), with and without trajectories (the
+# trajectory-free consumer interleaves the walks of a lane's rollouts and stores vectors).
+
+
 @pytest.mark.parametrize("case", [CASES[0], CASES[1], CASES[3], CASES[6]])
-def test_stream3_variant_is_bit_exact(ctx, oracle, case):
-    """k_stream3 (option stream3 = 1): the role-split variant of the fused kernel — recurrence, temper and walk in
-    separate warps handing off through mbarriers.  Slower than k_stream2 on B200 (profiles/README.md r1h), kept
-    selectable; it must give the same bytes."""
+@pytest.mark.parametrize("per_sm", [1, 4, 8, 16])
+@pytest.mark.parametrize("rb", [32, 64, 128])
+def test_stream_geometry_matrix(ctx, oracle, case, per_sm, rb):
     rows, cols, T, thr, depth, sseed, pre, tseed, bias, mseed, mpre = case
-    n = 5000
+    n = 70000 + 37 * per_sm + rb  # ragged tail: the last stream and its last batch are partial
     exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth,
                                       state_seed=sseed, state_pre_discard=pre, transition_seed=tseed, payoff_bias=bias,
                                       model_seed=mseed, model_pre_discard=mpre)
-    eng = Engine(mseed).discard(mpre)
-    ctx.set_option("stream3", 1)
+    ctx.set_option("streams_per_sm", per_sm)
+    ctx.set_option("rb", rb)
     try:
-        got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
-                       bias=bias, engine=eng)
+        for want_traj in (False, True):
+            eng = Engine(mseed).discard(mpre)
+            got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed,
+                           bias=bias, engine=eng, want_traj=want_traj)
+            assert ctx.last_path == "stream_table"
+            assert ctx.stat("last_streams") >= min(148 * per_sm, n // 128) * 0.5
+            check_same(got, exp, n)
+            assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
     finally:
-        ctx.set_option("stream3", 0)
+        ctx.set_option("streams_per_sm", 0)
+        ctx.set_option("rb", 32)
+
+
+@pytest.mark.parametrize("per_sm", [1, 8, 16])
+@pytest.mark.parametrize("rb", [32, 64, 128])
+def test_mold_geometry_matrix(ctx, oracle, per_sm, rb):
+    n, depth = 90001, 10
+    exp = loader.mold_rollouts(oracle, n, n_actions=2, depth=depth, model_seed=3, want_traj=False)
+    ctx.set_option("streams_per_sm", per_sm)
+    ctx.set_option("rb", rb)
+    try:
+        eng = Engine(3)
+        th = np.zeros(n, np.uint32)
+        sums = np.zeros(8, np.uint64)
+        ctx.rollout_mold(n, n_actions=2, depth=depth, engine=eng, traj_hash=th, sums=sums)
+        assert ctx.last_path == "stream_mold"
+    finally:
+        ctx.set_option("streams_per_sm", 0)
+        ctx.set_option("rb", 32)
+    assert np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
+    assert engine_matches(eng, 3, 4 * depth * n, oracle)
+
+
+def test_packed_payoffs_every_path(ctx, oracle):
+    """pcu_out.payoff_packed2: 2 bits per rollout, written by the fused kernel itself (one byte per lane) and by a
+    packing pass behind the general kernels; alone and next to the byte output."""
+    rng = np.random.default_rng(5)
+    for n in (33, 1001, 70003):
+        seeds = rng.integers(0, 2**63, n).astype(np.uint64)
+        cases = [
+            ("stream_table", dict(rows=3, cols=3, transitions=1, depth=10), {}),
+            ("stream_table", dict(rows=9, cols=9, transitions=3, depth=20), {}),
+            ("lane_private_S", dict(rows=3, cols=3, transitions=1, depth=10), dict(state_seed=seeds)),
+            ("warp_private_S", dict(rows=4, cols=3, transitions=2, depth=6), dict(state_seed=seeds, transition_seed=seeds)),
+        ]
+        for path, shape, extra in cases:
+            if path == "warp_private_S" and n > 2000:
+                continue
+            exp = loader.random_tree_rollouts(oracle, n, model_seed=2, want_traj=False, **shape, **extra)
+            for with_bytes in (False, True):
+                packed = np.full((n + 3) // 4, 255, np.uint8)
+                pay = np.full(n, 255, np.uint8) if with_bytes else None
+                sums = np.zeros(8, np.uint64)
+                ctx.rollout_random_tree(n, engine=Engine(2), payoff=pay, payoff_packed=packed, sums=sums, **shape, **extra)
+                assert ctx.last_path == path
+                assert np.array_equal(unpack2(packed, n), exp["payoff"]), (path, n, with_bytes)
+                if n % 4:
+                    assert packed[-1] >> (2 * (n % 4)) == 0  # unused bit pairs of the last byte are zero
+                if with_bytes:
+                    assert np.array_equal(pay, exp["payoff"])
+                assert np.array_equal(sums, exp["sums"])
+    packed = np.full(26, 255, np.uint8)
+    ctx.rollout_mold(101, n_actions=3, depth=4, engine=Engine(0), payoff_packed=packed)
+    assert not packed.any()
+
+
+def test_packed_payoffs_zero_copy(ctx, oracle):
+    """>= 2^20 rollouts into pinned memory: the packed bytes are stored straight over PCIe by the consumer warps."""
+    n = (1 << 21) + 777
+    ref = np.zeros(n, np.uint8)
+    ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, engine=Engine(7), payoff=ref)
+    packed = ctx.pinned((n + 3) // 4, np.uint8)
+    packed[:] = 255
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_random_tree(n, rows=3, cols=3, depth=10, engine=Engine(7), payoff_packed=packed, sums=sums)
+    assert np.array_equal(unpack2(packed, n), ref)
+    assert np.bincount(ref, minlength=3).tolist() == [int(sums[2]), int(sums[1]), int(sums[0])]
+
+
+def test_trajectory_stride_shorter_than_depth(ctx, oracle):
+    """A per-rollout depth array with depth[i] > traj_stride: the extra steps are played and hashed but not recorded
+    (the oracle clamps the same way); nothing is written past a rollout's traj_stride slots."""
+    rng = np.random.default_rng(11)
+    for n, kw, path in ((20, dict(), "small_tree"),
+                        (500, dict(state_seed=rng.integers(0, 2**63, 500).astype(np.uint64)), "lane_private_S"),
+                        (500, dict(state_seed=rng.integers(0, 2**63, 500).astype(np.uint64), T=2), "warp_private_S")):
+        T = kw.pop("T", 1)
+        depth = rng.integers(1, 9, n).astype(np.uint32)
+        stride = 4
+        exp = loader.random_tree_rollouts(oracle, n, rows=3, cols=3, transitions=T, depth=depth, model_seed=6, **kw)
+        exp_traj = exp["traj"][:, :stride, :]
+        traj = np.full((n + 1, stride, 3), 77, np.uint8)  # one guard row behind the buffer
+        th = np.zeros(n, np.uint32)
+        ctx.rollout_random_tree(n, rows=3, cols=3, transitions=T, depth=depth.astype(np.uint16), engine=Engine(6), traj=traj,
+                                traj_stride=stride, traj_hash=th, **kw)
+        assert ctx.last_path == path
+        assert np.array_equal(traj[:n], exp_traj), path
+        assert (traj[n] == 77).all()
+        assert np.array_equal(th, exp["traj_hash"])
+    depth = rng.integers(1, 9, 300).astype(np.uint32)
+    exp = loader.mold_rollouts(oracle, 300, n_actions=3, depth=depth, model_seed=6)
+    traj = np.full((301, 4, 3), 77, np.uint8)
+    ctx.rollout_mold(300, n_actions=3, depth=depth.astype(np.uint16), engine=Engine(6), traj=traj, traj_stride=4)
+    assert np.array_equal(traj[:300], exp["traj"][:, :4, :]) and (traj[300] == 77).all()
+
+
+def test_general_path_rejects_low_positions(ctx):
+    """state_pos arrays are range-checked on every path, not only the fused one (k_warp would index its engine below 0)."""
+    n = 200
+    pos = np.full(n, 2 * 3 * 3 * 2, np.uint32)
+    pos[77] = 5
+    seeds = np.arange(n, dtype=np.uint64)
+    with pytest.raises(PcuError) as e:
+        ctx.rollout_random_tree(n, rows=3, cols=3, transitions=2, depth=4, state_seed=seeds, state_pos=pos, engine=Engine(0),
+                                payoff=np.zeros(n, np.uint8))
+    assert e.value.code == -1
+    eng = Engine(0)
+    before = [eng.copy().next() for _ in range(3)]
+    with pytest.raises(PcuError):
+        ctx.rollout_random_tree(n, rows=3, cols=3, transitions=2, depth=4, state_seed=seeds, state_pos=pos, engine=eng,
+                                payoff=np.zeros(n, np.uint8))
+    assert [eng.copy().next() for _ in range(3)] == before  # a refused call leaves the caller's engine alone
+
+
+def _windows(n, chunk, count):
+    """Window starts that straddle stream-chunk boundaries (first + k * chunk +- a little), plus the two ends."""
+    starts = {0, n - count}
+    streams = (n + chunk - 1) // chunk
+    for k in (1, streams // 3, streams - 1):
+        if 0 < k < streams:
+            starts.add(max(0, min(n - count, k * chunk - count // 2)))
+    return sorted(starts)
+
+
+@pytest.mark.parametrize("log2n", [24, 26])
+def test_full_size_config_b(ctx, oracle, log2n):
+    """BASELINE configs[2]: RandomTree depth 20, 9x9 actions, 3 chance transitions — 2^24 (one GPU's bench batch) and
+    2^26 (the config as written).  These sizes run 8 model streams per SM (run_stream's auto rule), the geometry every
+    config-3 number rides on.  Exact counts, oracle windows straddling stream-chunk boundaries, and the post-batch
+    engine against the host jump-ahead."""
+    n = 1 << log2n
+    depth = 20
+    eng = Engine(0)
+    payoff = np.zeros(n, np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_random_tree(n, rows=9, cols=9, transitions=3, depth=depth, engine=eng, payoff=payoff, traj_hash=th, sums=sums)
     assert ctx.last_path == "stream_table"
-    check_same(got, exp, n)
-    assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
+    chunk, streams = int(ctx.stat("last_chunk")), int(ctx.stat("last_streams"))
+    assert streams > 148 * 4  # more than four streams per SM: the 8-per-SM geometry
+    assert int(sums[:3].sum()) == n and int(sums[3]) == depth * n
+    assert np.bincount(payoff, minlength=3).tolist() == [int(sums[2]), int(sums[1]), int(sums[0])]
+    assert int(th.astype(np.uint64).sum()) == int(sums[4])
+    assert np.bincount(payoff[:20000], minlength=3).tolist() == [8927, 2124, 8949]  # Appendix B2 prefix
+    count = 768
+    for start in _windows(n, chunk, count):
+        loader.set_model_engine(oracle, Engine(0).discard(4 * depth * start))
+        exp = loader.random_tree_rollouts(oracle, count, rows=9, cols=9, transitions=3, depth=depth, want_traj=False)
+        assert np.array_equal(payoff[start:start + count], exp["payoff"]), start
+        assert np.array_equal(th[start:start + count], exp["traj_hash"]), start
+    ref = Engine(0).discard(4 * depth * n)
+    assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
+
+
+def test_full_size_mold_share_of_config_4(ctx, oracle):
+    """BASELINE configs[3]: MoldState{2, 10}, 2^28 rollouts over 8 GPUs = 2^25 per GPU (8 streams per SM)."""
+    n, depth = 1 << 25, 10
+    eng = Engine(0)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_mold(n, n_actions=2, depth=depth, engine=eng, traj_hash=th, sums=sums)
+    assert ctx.last_path == "stream_mold"
+    chunk, streams = int(ctx.stat("last_chunk")), int(ctx.stat("last_streams"))
+    assert streams > 148 * 4
+    assert sums[:5].tolist() == [0, n, 0, depth * n, int(th.astype(np.uint64).sum())]
+    count = 4096
+    for start in _windows(n, chunk, count):
+        loader.set_model_engine(oracle, Engine(0).discard(4 * depth * start))
+        exp = loader.mold_rollouts(oracle, count, n_actions=2, depth=depth, want_traj=False)
+        assert np.array_equal(th[start:start + count], exp["traj_hash"]), start
+    ref = Engine(0).discard(4 * depth * n)
+    assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
+
+
+def test_state_table_is_cached_by_covering_range(ctx, oracle):
+    """Leaf batches of one search share the root's state seed but move their position range from call to call: the
+    state-stream table is rebuilt only when a batch leaves the range the cached one covers."""
+    rng = np.random.default_rng(2)
+    n = 4096
+    built = []
+    for lo, hi in ((0, 200), (50, 150), (0, 200), (100, 260), (30, 250)):
+        pre = rng.integers(lo, hi, n).astype(np.uint32)
+        exp = loader.random_tree_rollouts(oracle, n, rows=3, cols=3, depth=6, state_seed=9, state_pre_discard=pre,
+                                          model_seed=1, want_traj=False)
+        got = run_tree(ctx, n, rows=3, cols=3, depth=6, state_seed=9, pre=pre, engine=Engine(1), want_traj=False)
+        assert ctx.last_path == "stream_table"
+        check_same(got, exp, n)
+        built.append(ctx.stat("last_table_build_ms") > 0)
+    assert built == [True, False, False, True, False]
+
+
+# ---------------------------------------------------------------------------------------------
+# One context over several GPUs (pcu_create_multi).  On a one-GPU box the shards share GPU 0 (listing a device twice is
+# allowed for exactly this): the shard plan, the per-shard slices of the global jump family, the output offsets and the
+# post-batch engine are the same code; only the reduction differs (a summing kernel instead of ncclAllReduce).
+
+
+def _multi_ids():
+    import torch
+
+    k = torch.cuda.device_count()
+    return list(range(k)) if k >= 2 else [0, 0, 0]
+
+
+@pytest.fixture(scope="module")
+def mctx():
+    c = Context(_multi_ids())
+    c.set_option("multi_min_rollouts", 1000)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("case", [CASES[0], CASES[1], CASES[3]])
+def test_multi_gpu_context_equals_single(ctx, mctx, oracle, case):
+    rows, cols, T, thr, depth, sseed, pre, tseed, bias, mseed, mpre = case
+    n = 200000 + 77
+    kw = dict(rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=sseed, pre=pre, tseed=tseed, bias=bias)
+    e1, e2 = Engine(mseed).discard(mpre), Engine(mseed).discard(mpre)
+    one = run_tree(ctx, n, engine=e1, want_traj=False, **kw)
+    many = run_tree(mctx, n, engine=e2, want_traj=False, **kw)
+    assert mctx.last_path.startswith("stream_table x") and mctx.device_count >= 2
+    check_same(many, one, n)
+    assert np.array_equal(e1.x, e2.x) and int(e1.p[0]) == int(e2.p[0])  # the caller's engine: byte for byte
+    exp = loader.random_tree_rollouts(oracle, 3000, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth,
+                                      state_seed=sseed, state_pre_discard=pre, transition_seed=tseed, payoff_bias=bias,
+                                      model_seed=mseed, model_pre_discard=mpre, want_traj=False)
+    assert np.array_equal(many["payoff"][:3000], exp["payoff"])
+
+
+def test_multi_gpu_context_general_paths(ctx, mctx, oracle):
+    """Distinct roots (uniform depth: shards are slices of one family of code streams), ragged depths (per-shard
+    engines advanced on the host), mode P, MoldState, packed output and trajectories across shard boundaries."""
+    rng = np.random.default_rng(13)
+    n = 30011
+    seeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    depth = rng.integers(1, 12, n).astype(np.uint32)
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    for kw, engine_words in (
+        (dict(rows=3, cols=3, depth=10, state_seed=seeds), 40 * n),
+        (dict(rows=3, cols=3, depth=depth, state_seed=seeds), 4 * int(depth.sum())),
+        (dict(rows=4, cols=3, transitions=2, depth=depth, state_seed=seeds, transition_seed=seeds), 4 * int(depth.sum())),
+        (dict(rows=3, cols=3, depth=10, state_seed=seeds, model_seeds=mseeds), 0),
+    ):
+        ms = kw.pop("model_seeds", None)
+        exp = loader.random_tree_rollouts(oracle, n, model_seed=5, model_seeds=ms, want_traj=True, **kw)
+        d = kw.pop("depth")
+        dmax = int(d) if np.isscalar(d) else int(d.max())
+        payoff = np.full(n, 255, np.uint8)
+        packed = np.zeros((n + 3) // 4, np.uint8)
+        traj = np.zeros((n, dmax, 3), np.uint8)
+        th = np.zeros(n, np.uint32)
+        sums = np.zeros(8, np.uint64)
+        eng = None if ms is not None else Engine(5)
+        mctx.rollout_random_tree(n, depth=d if np.isscalar(d) else d.astype(np.uint16), engine=eng, model_seeds=ms,
+                                 payoff=payoff, payoff_packed=packed, traj=traj, traj_stride=dmax, traj_hash=th, sums=sums, **kw)
+        assert " x" in mctx.last_path, mctx.last_path
+        assert np.array_equal(payoff, exp["payoff"]) and np.array_equal(unpack2(packed, n), exp["payoff"])
+        assert np.array_equal(traj, exp["traj"]) and np.array_equal(th, exp["traj_hash"])
+        assert np.array_equal(sums, exp["sums"])
+        if eng is not None:
+            assert engine_matches(eng, 5, engine_words, oracle)
+    exp = loader.mold_rollouts(oracle, n, n_actions=3, depth=depth, model_seed=6, want_traj=False)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    eng = Engine(6)
+    mctx.rollout_mold(n, n_actions=3, depth=depth.astype(np.uint16), engine=eng, traj_hash=th, sums=sums)
+    assert np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
+    assert engine_matches(eng, 6, 4 * int(depth.sum()), oracle)
+    exp = loader.mold_rollouts(oracle, n, n_actions=2, depth=10, model_seed=6, want_traj=False)
+    eng = Engine(6)
+    mctx.rollout_mold(n, n_actions=2, depth=10, engine=eng, traj_hash=th, sums=sums)
+    assert mctx.last_path.startswith("stream_mold x")
+    assert np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
+    assert engine_matches(eng, 6, 40 * n, oracle)
+
+
+def test_multi_gpu_small_batches_stay_on_first_gpu(mctx, oracle):
+    mctx.set_option("multi_min_rollouts", 1 << 16)
+    try:
+        exp = loader.random_tree_rollouts(oracle, 500, rows=3, cols=3, depth=10, want_traj=False)
+        got = run_tree(mctx, 500, rows=3, cols=3, depth=10, engine=Engine(0), want_traj=False)
+        assert mctx.last_path == "stream_table"
+        check_same(got, exp, 500)
+    finally:
+        mctx.set_option("multi_min_rollouts", 1000)
+
+
+def test_warmup_pays_the_family_build(ctx):
+    """pcu_warmup builds the jump-polynomial family a batch shape needs; the call after it finds it cached."""
+    n, depth = 3_000_000 + 12800, 7  # a stride no other test uses
+    ctx.warmup(n, depth)
+    sums = np.zeros(8, np.uint64)
+    ctx.rollout_mold(n, n_actions=2, depth=depth, engine=Engine(0), sums=sums)
+    assert ctx.stat("last_family_build_ms") == 0.0
+    ctx.rollout_mold(n + 40 * 12800, n_actions=2, depth=depth, engine=Engine(0), sums=sums)  # a new stride: built in the call
+    assert ctx.stat("last_family_build_ms") > 0.0
 
 
 @pytest.mark.parametrize("args", [("80", "7"), ("80", "8", "lane")])
