@@ -32,11 +32,9 @@ sys.path.insert(0, str(ROOT))
 
 WORKLOADS = {
     # name: (kind, rows, cols, transitions, depth, log2 n per gpu, algorithmic int32 ops/step, ops/rollout setup)
-    # traffic: dram__bytes_read.sum + dram__bytes_write.sum of k_stream2 from the ncu --set full capture of this build
-    # (profiles/r1i_ncu_full_summary.csv, 2^24 rollouts): 1.53 MB read, 0 written — under ncu the 16.8 MB of payoff
-    # bytes were still in L2 when the kernel ended; they reach HBM later (or go straight to the host when zero-copy).
+    # roofline.traffic comes from profiles/traffic.json (an ncu --set full capture of THESE sources) or is null
     "tree_d10_3x3x1": dict(kind="tree", rows=3, cols=3, T=1, depth=10, log2n=24, ops_step=318.0, ops_exec=76.0,
-                           kernel="k_stream2<TREE,u8,tab_smem>", traffic=1528320.0),
+                           kernel="k_stream2<TREE,u8,tab_smem>"),
     "tree_d20_9x9x3": dict(kind="tree", rows=9, cols=9, T=3, depth=20, log2n=24, ops_step=4920.0, ops_exec=80.0,
                            kernel="k_stream2<TREE,u8,tab_smem>"),
     # distinct roots (state_seed_i = i): every rollout owns a private state engine, so the
@@ -290,187 +288,368 @@ def run_search(args):
 
 # ------------------------------------------------------------------------------ our arm
 
+CSRC = ROOT / "pinyon_b200" / "csrc"
 
-def run_ours(args, w):
-    import torch
-    import torch.distributed as dist
 
-    from pinyon_b200 import Context, Engine, sharding
+def source_hash():
+    """Hash of the kernel sources: an ncu capture under profiles/ speaks for this build only if it recorded the same one."""
+    import hashlib
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    ctx = Context(local)
-    if args.streams_per_sm:
-        ctx.set_option("streams_per_sm", args.streams_per_sm)
-    if args.no_zero_copy:
-        ctx.set_option("zero_copy", 0)
-    n = 1 << (args.log2n or w["log2n"])
+    h = hashlib.sha256()
+    for path in sorted(CSRC.glob("*")):
+        if path.suffix in {".cu", ".cuh", ".h", ".cpp"}:
+            h.update(path.read_bytes())
+    return h.hexdigest()[:16]
+
+
+def measured_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of the dominant kernel, from an `ncu --set full` capture
+    summarised in profiles/traffic.json by tools/ncu_summary.py — only if it was taken on these very sources."""
+    path = ROOT / "profiles" / "traffic.json"
+    if not path.exists():
+        return None, None
+    try:
+        rec = json.loads(path.read_text()).get(workload)
+    except ValueError:
+        return None, None
+    if not rec or rec.get("source_hash") != source_hash():
+        return None, None
+    return float(rec["dram_bytes"]), rec.get("capture")
+
+
+class Rig:
+    """One rank: its GPU, its context, the NCCL group, and the timing protocol of the bench contract."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+
+        from pinyon_b200 import Context
+
+        self.torch, self.dist, self.args = torch, dist, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if self.world > 1:
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        t0 = time.perf_counter()
+        self.ctx = Context(self.local)
+        self.create_ms = 1e3 * (time.perf_counter() - t0)
+        if args.streams_per_sm:
+            self.ctx.set_option("streams_per_sm", args.streams_per_sm)
+        if args.rb:
+            self.ctx.set_option("rb", args.rb)
+        if args.no_zero_copy:
+            self.ctx.set_option("zero_copy", 0)
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)  # > 126 MB L2
+        self.stream = torch.cuda.current_stream()
+        self.ctx.set_stream(self.stream.cuda_stream)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def reduce(self, values, op="max"):
+        t = self.torch.tensor(values, dtype=self.torch.float64 if op == "max" else self.torch.int64, device=self.dev)
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX if op == "max" else self.dist.ReduceOp.SUM)
+        return t.cpu().tolist()
+
+    def close(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
+        self.ctx.close()
+
+
+def measure(rig, w, n, steps, warmup, packed=False, sample_clocks=False):
+    """W warm-up steps, then exactly `steps` timed steps of workload `w` with n rollouts on this rank: device-resident
+    (CUDA events, L2 flushed between steps) and end to end through the C ABI with host buffers; max over ranks."""
+    torch, ctx = rig.torch, rig.ctx
+    from pinyon_b200 import Engine, sharding
+
     depth = w["depth"]
-
-    # this rank's slice of the one global model stream: rollouts [rank*n, (rank+1)*n)
-    shard = sharding.plan(n * world, world, rank, depth)
-    assert shard.count == n
+    shard = sharding.plan(n * rig.world, rig.world, rig.rank, depth)  # this rank's slice of the ONE global model stream
     base_engine = Engine(0).discard(shard.engine_offset)
-
-    payoff_d = torch.empty(n, dtype=torch.uint8, device=dev)
-    sums_d = torch.zeros(8, dtype=torch.int64, device=dev)
-    payoff_h = ctx.pinned(n, np.uint8)
+    payoff_d = torch.empty(n, dtype=torch.uint8, device=rig.dev)
+    sums_d = torch.zeros(8, dtype=torch.int64, device=rig.dev)
+    payoff_h = ctx.pinned((n + 3) // 4 if packed else n, np.uint8)
     sums_h = np.zeros(8, np.uint64)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    stream = torch.cuda.current_stream()
-    ctx.set_stream(stream.cuda_stream)
-
     dr_dev, dr_host = {}, {}
     if w.get("dr"):
-        first = shard.first
-        idx = np.arange(first, first + n, dtype=np.uint64)
-        ts = idx * np.uint64(0x9E3779B97F4A7C15)
+        idx = np.arange(shard.first, shard.first + n, dtype=np.uint64)
         dr_host = dict(state_seed=ctx.pinned(n, np.uint64), transition_seed=ctx.pinned(n, np.uint64))
         dr_host["state_seed"][:] = idx
-        dr_host["transition_seed"][:] = ts
-        dr_dev = {k: torch.from_numpy(v.view(np.int64)).to(dev) for k, v in dr_host.items()}
+        dr_host["transition_seed"][:] = idx * np.uint64(0x9E3779B97F4A7C15)
+        dr_dev = {k: torch.from_numpy(v.view(np.int64)).to(rig.dev) for k, v in dr_host.items()}
 
-    def call(payoff, sums):
+    def call(payoff, sums, host):
         eng = base_engine.copy()
+        out = dict(payoff_packed=payoff) if (host and packed) else dict(payoff=payoff)
         if w["kind"] == "tree":
-            extra = dr_dev if isinstance(payoff, torch.Tensor) else dr_host
-            ctx.rollout_random_tree(n, rows=w["rows"], cols=w["cols"], transitions=w["T"], depth=depth, engine=eng,
-                                    payoff=payoff, sums=sums, **extra)
+            ctx.rollout_random_tree(n, rows=w["rows"], cols=w["cols"], transitions=w["T"], depth=depth, engine=eng, sums=sums,
+                                    **out, **(dr_host if host else dr_dev))
         else:
-            ctx.rollout_mold(n, n_actions=w["rows"], depth=depth, engine=eng, payoff=payoff, sums=sums)
+            ctx.rollout_mold(n, n_actions=w["rows"], depth=depth, engine=eng, sums=sums, **out)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- device-resident timing (value)
-    for _ in range(args.warmup):
-        flush.zero_()
-        call(payoff_d, sums_d)
-    barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
-    # nvidia-smi takes up to a second to attach to the driver, and launches stall while it does: wait for its first
-    # sample so that only steady 100 ms polling overlaps the timed region (a 1.66 ms outlier step was seen otherwise)
-    t_wait = time.time()
-    while not sampler.rows and time.time() - t_wait < 3.0:
-        time.sleep(0.05)
-    time.sleep(0.1)
+    t_cold = time.perf_counter()
+    call(payoff_d, sums_d, False)
+    torch.cuda.synchronize()
+    cold_ms = 1e3 * (time.perf_counter() - t_cold)  # first call of this shape: jump-family build, table build, allocations
+    cold = dict(first_call_ms=cold_ms, family_build_ms=ctx.stat("last_family_build_ms"),
+                table_build_ms=ctx.stat("last_table_build_ms"))
+    for _ in range(max(warmup - 1, 0)):
+        rig.flush.zero_()
+        call(payoff_d, sums_d, False)
+    rig.barrier()
+    sampler = None
+    if sample_clocks:
+        sampler = ClockSampler(rig.local)
+        sampler.start()
+        # nvidia-smi takes up to a second to attach to the driver, and launches stall while it does: wait for its first
+        # sample so that only steady 100 ms polling overlaps the timed region
+        t_wait = time.time()
+        while not sampler.rows and time.time() - t_wait < 3.0:
+            time.sleep(0.05)
+        time.sleep(0.1)
     launches0 = ctx.launches
-    starts = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    ends = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
-    barrier()
+    starts = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ends = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    rig.barrier()
     t_wall0 = time.time()
     kernel_ms = []
-    for i in range(args.steps):
-        flush.zero_()
-        starts[i].record(stream)
-        call(payoff_d, sums_d)
-        ends[i].record(stream)
+    for i in range(steps):
+        rig.flush.zero_()
+        starts[i].record(rig.stream)
+        call(payoff_d, sums_d, False)
+        ends[i].record(rig.stream)
         kernel_ms.append(ctx.last_kernel_ms)  # the rollout kernel alone: CUDA events on the launching stream
-    barrier()
+    rig.barrier()
     t_wall1 = time.time()
     launches = ctx.launches - launches0
     dev_ms = sum(s.elapsed_time(e) for s, e in zip(starts, ends))
-    clocks = sampler.stop(t_wall0, t_wall1)
-    sums_host = sums_d.cpu().numpy().view(np.uint64).copy()
+    clocks = sampler.stop(t_wall0, t_wall1) if sampler else None
+    sums_dev = sums_d.cpu().numpy().view(np.uint64).copy()
+    path = ctx.last_path
+    geometry = dict(streams=int(ctx.stat("last_streams")), chunk=int(ctx.stat("last_chunk")))
 
-    # ---- end-to-end timing through the C ABI with host buffers
-    for _ in range(min(args.warmup, 3)):
-        call(payoff_h, sums_h)
-    barrier()
+    # ---- end to end through the C ABI with host buffers
+    for _ in range(min(warmup, 3)):
+        call(payoff_h, sums_h, True)
+    rig.barrier()
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        call(payoff_h, sums_h)
+    for _ in range(steps):
+        call(payoff_h, sums_h, True)
     torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    assert np.array_equal(sums_h, sums_host), "host and device paths disagree"
+    e2e_ms = 1e3 * (time.perf_counter() - t0)
+    assert np.array_equal(sums_h, sums_dev), "host and device paths disagree"
     assert int(sums_h[:3].sum()) == n
 
-    t = torch.tensor([dev_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
-    tot = torch.from_numpy(sums_host.astype(np.int64)).to(dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)  # the path's only collective: W/D/L/step sums over NVLink
-    dev_ms, e2e_ms = t.tolist()
-    totals = tot.cpu().numpy()
+    dev_ms, e2e_ms = rig.reduce([dev_ms, e2e_ms], "max")
+    totals = rig.reduce(sums_dev.astype(np.int64).tolist(), "sum")  # the path's only collective: counters over NVLink
+    h2d = 624 * 4 + 8
+    if w.get("dr"):
+        h2d += 8 * n * (2 if w["T"] > 1 else 1)  # state seeds (+ transition seeds when transitions > 1)
+    return dict(n=n, steps=steps, dev_ms=dev_ms, e2e_ms=e2e_ms, kernel_ms=float(np.mean(kernel_ms)), launches=int(launches),
+                clocks=clocks, totals=totals, path=path, geometry=geometry, cold=cold, h2d=h2d,
+                d2h=(len(payoff_h)) + 64 + 624 * 4)
+
+
+def roofline(w, m, int_peak, int_peak_alu, peaks, peak_kind, workload_name):
+    depth, n, k_ms = w["depth"], m["n"], m["kernel_ms"]
+    ops_launch = (w["ops_step"] * depth + w.get("ops_setup", 0.0)) * n   # SURVEY.md §8(d) algorithmic figure
+    exe_launch = w["ops_exec"] * depth * n                                 # what the kernel really has to do
+    achieved = ops_launch / (k_ms * 1e-3)
+    executed = exe_launch / (k_ms * 1e-3)
+    hbm_bytes = float(n)  # one payoff byte per rollout; inputs are batch-uniform scalars
+    if w.get("dr"):
+        hbm_bytes = float(n) * (1 + 8 + depth + 8)  # payoff + state seed + action codes + x[397] write/read
+    note = ("achieved = algorithmic int32 ops (SURVEY.md 8(d): %.0f per rollout-step, counted for a PRIVATE state "
+            "stream) / the rollout kernel's own CUDA-event time; peak = int-issue microbenchmark measured in this "
+            "run (LOP3 only %.1f, LOP3:IMAD 1:1 %.1f Gop/s). " % (w["ops_step"], int_peak_alu / 1e9, int_peak / 1e9))
+    if w.get("dr"):
+        note += ("DISTINCT-ROOT run: every rollout seeds and advances its own state engine (+%.0f ops per rollout "
+                 "for the seeding chains, included in achieved); `executed` counts the %.0f ops per rollout the "
+                 "kernels really issue. kernel_ms brackets the seeding pre-kernel + the rollout kernel (%s); the "
+                 "model-stream code generator (k_gen_codes2 + jump-ahead) runs before it and is in ms_per_step only"
+                 % (w["ops_setup"], w["ops_exec"] * depth, w["kernel"]))
+    else:
+        note += ("SHARED-STREAM run: every rollout of the batch shares the root's state seed, so the kernel serves "
+                 "the state stream from a shared-memory table and only has to generate the model stream: frac is "
+                 "computed on the algorithmic figure as the contract asks and exceeds what the kernel executes; "
+                 "`executed` counts the %.0f ops per step it really issues (4 words x (4 twist + 8 temper) + 2 u64 "
+                 "mod n x 9 + table walk) and executed.frac / frac_of_alu_pipe are the figures that measure the "
+                 "kernel" % w["ops_exec"])
+    traffic, capture = measured_traffic(workload_name)
+    return {"bound": "int_issue", "kernel": w["kernel"], "kernel_ms": k_ms,
+            "kernel_share_of_step": k_ms / (m["dev_ms"] / m["steps"]),
+            "achieved": achieved / 1e9, "peak": int_peak / 1e9, "unit": "Gop/s", "frac": achieved / int_peak,
+            "traffic": traffic, "traffic_source": capture,
+            "executed": {"ops_per_step": w["ops_exec"], "achieved": executed / 1e9, "frac": executed / int_peak,
+                         "frac_of_alu_pipe": executed / int_peak_alu},
+            "note": note,
+            "hbm": {"achieved": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                    "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"], "peak_source": peak_kind}}
+
+
+# Secondary workloads measured in the same run (BASELINE configs[2..4] and SURVEY 8(d)'s distinct-root runs): name,
+# workload key, log2 of the TOTAL batch (strong scaling: divided over the ranks) or None for the workload's per-GPU size.
+EXTRA = [
+    ("B_tree_d20_9x9x3_2p26", "tree_d20_9x9x3", 26),
+    ("M_mold_2_10_2p28", "mold_2_10", 28),
+    ("M1_DR_tree_d10_3x3x1", "tree_d10_3x3x1_dr", None),
+    ("M2_DR_tree_d20_9x9x3", "tree_d20_9x9x3_dr", None),
+]
+
+
+def single_process_line(args, w, world, depth):
+    """The same global batch through ONE context over all N GPUs (pcu_create_multi: shards, per-shard jump slices and the
+    NCCL all-reduce live inside the library) — what `Types::Model model{prng{0}}` + model.inference(batch) gets."""
+    import torch
+
+    from pinyon_b200 import Context, Engine
+
+    n = (1 << (args.log2n or w["log2n"])) * world
+    ctx = Context(list(range(world)))
+    payoff = ctx.pinned(n, np.uint8)
+    packed = ctx.pinned((n + 3) // 4, np.uint8)
+    sums = np.zeros(8, np.uint64)
+
+    def call(**out):
+        eng = Engine(0)
+        if w["kind"] == "tree":
+            ctx.rollout_random_tree(n, rows=w["rows"], cols=w["cols"], transitions=w["T"], depth=depth, engine=eng, sums=sums, **out)
+        else:
+            ctx.rollout_mold(n, n_actions=w["rows"], depth=depth, engine=eng, sums=sums, **out)
+
+    res = {}
+    for name, out in (("bytes", dict(payoff=payoff)), ("packed2", dict(payoff_packed=packed)), ("sums_only", dict())):
+        for _ in range(3):
+            call(**out)
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            call(**out)
+        sec = time.perf_counter() - t0
+        res[name] = n * args.steps / sec
+    path = ctx.last_path
+    nccl = ctx.stat("nccl_calls")
+    ctx.close()
+    torch.cuda.synchronize()
+    return {"e2e_rollouts_per_s": res["bytes"], "e2e_packed2_rollouts_per_s": res["packed2"],
+            "e2e_sums_only_rollouts_per_s": res["sums_only"], "rollouts_per_step": n, "path": path, "nccl_all_reduces": nccl,
+            "note": "one process, one pcu_create_multi context over all GPUs, host buffers (pinned), wall clock around "
+                    "the calls; the rank-per-GPU figures above are the bench contract's form"}
+
+
+def run_ours(args, w, workload_name):
+    rig = Rig(args)
+    world, rank = rig.world, rig.rank
+    n = 1 << (args.log2n or w["log2n"])
+    depth = w["depth"]
+    m = measure(rig, w, n, args.steps, args.warmup, sample_clocks=True)
+    packed_m = measure(rig, w, n, max(3, args.steps // 2), 3, packed=True) if not w.get("dr") else None
+
+    extras = {}
+    if not args.no_extra:
+        for name, key, log2total in EXTRA:
+            if key == workload_name:
+                continue
+            we = WORKLOADS[key]
+            ne = (1 << log2total) // world if log2total else 1 << we["log2n"]
+            em = measure(rig, we, ne, max(3, min(args.steps, 5)), 3)
+            extras[name] = (we, em, "strong" if log2total else "weak", key)
+
+    search = None
+    if not args.no_extra and SEARCH_BIN.exists():
+        try:
+            rig.barrier()
+            mine = run_search_binary("gpu", rig.local, rank, 4096, 10, 2)
+            sec = rig.reduce([mine["seconds"]], "max")[0]
+            search = {"metric": "search leaves/sec", "value": 4096 * 10 * world / sec, "unit": "leaves/s",
+                      "config": "OffPolicy<Exp3<GpuModel<RandomTree 3x3x1 d10>>>, 4096 leaves per batched inference, "
+                                "one tree per GPU (root-parallel)", "ms_per_step": 1e3 * sec / 10}
+            if rank == 0:
+                ref = run_search_binary("ref", 0, 0, 4096, 5, 1)
+                search["reference_single_thread_leaves_per_s"] = ref["leaves_per_s"]
+        except Exception as exc:  # the search line is extra evidence; the headline must still print
+            search = {"error": str(exc)[:300]}
+
+    single = None
+    if world > 1 and not args.no_extra:
+        rig.barrier()
+        if rank == 0:
+            try:
+                single = single_process_line(args, w, world, depth)
+            except Exception as exc:
+                single = {"error": str(exc)[:300]}
+        rig.barrier()
 
     if rank == 0:
+        ctx = rig.ctx
         peaks, peak_kind = measured_peaks()
-        total_rollouts = float(n) * world * args.steps
-        value = total_rollouts / (dev_ms * 1e-3)
-        e2e = total_rollouts / (e2e_ms * 1e-3)
         # integer-issue peaks measured in this run (pcu_measure_int_peak): LOP3 only (ALU pipe), and
         # LOP3:IMAD 1:1 (ALU + FMA pipes together: the issue-rate ceiling of sm_100 for int32 work)
         int_peak_alu = ctx.int_peak(0, 5)
         int_peak = max(ctx.int_peak(5, 5), ctx.int_peak(2, 5), int_peak_alu)
-        ms_step = dev_ms / args.steps
-        k_ms = float(np.mean(kernel_ms))
-        ops_launch = (w["ops_step"] * depth + w.get("ops_setup", 0.0)) * n   # SURVEY.md §8(d) algorithmic figure
-        exe_launch = w["ops_exec"] * depth * n          # what the kernel really has to do
-        achieved = ops_launch / (k_ms * 1e-3)
-        executed = exe_launch / (k_ms * 1e-3)
-        hbm_bytes = float(n)  # one payoff byte per rollout; inputs are batch-uniform scalars
-        h2d = 624 * 4 + 8
-        if w.get("dr"):
-            hbm_bytes = float(n) * (1 + 8 + depth + 8)  # payoff + state seed + action codes + x[397] write/read
-            h2d += 8 * n * (2 if w["T"] > 1 else 1)  # state seeds (+ transition seeds when transitions > 1)
-        note = ("achieved = algorithmic int32 ops (SURVEY.md 8(d): %.0f per rollout-step, counted for a PRIVATE state "
-                "stream) / the rollout kernel's own CUDA-event time; peak = int-issue microbenchmark measured in this "
-                "run (LOP3 only %.1f, LOP3:IMAD 1:1 %.1f Gop/s). " % (w["ops_step"], int_peak_alu / 1e9, int_peak / 1e9))
-        if w.get("dr"):
-            note += ("DISTINCT-ROOT run: every rollout seeds and advances its own state engine (+%.0f ops per rollout "
-                     "for the seeding chains, included in achieved); `executed` counts the %.0f ops per rollout the "
-                     "kernels really issue. kernel_ms brackets the seeding pre-kernel + the rollout kernel (%s); the "
-                     "model-stream code generator (k_gen_codes2 + jump-ahead) runs before it and is in ms_per_step only"
-                     % (w["ops_setup"], w["ops_exec"] * depth, w["kernel"]))
-        else:
-            note += ("SHARED-STREAM run: every rollout of the batch shares the root's state seed, so the kernel serves "
-                     "the state stream from a shared-memory table and only has to generate the model stream: "
-                     "`executed` counts those %.0f ops per step (4 words x (4 twist + 8 temper) + 2 u64 mod n x 9 + "
-                     "table walk) and is the figure that measures the kernel; frac > executed.frac is the shortcut's "
-                     "gain, not kernel quality" % w["ops_exec"])
+        total_rollouts = float(n) * world * args.steps
+        value = total_rollouts / (m["dev_ms"] * 1e-3)
+        e2e = total_rollouts / (m["e2e_ms"] * 1e-3)
         line = {
             "metric": "rollouts/sec", "value": value, "unit": "rollouts/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": m["dev_ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": describe(w, n), "l2": "flushed between steps by a 256 MiB device write",
                        "parallelism": f"dp{world}: rollout-index shards of one model stream, NCCL all-reduce of sums only",
-                       "streams_per_sm": args.streams_per_sm or ("auto: 8 from 2.5e8 rollout-steps per call, else 4")},
+                       "streams_per_sm": args.streams_per_sm or ("auto: 8 from 2.5e8 rollout-steps per call, else 4"),
+                       "kernel_path": m["path"], "model_streams": m["geometry"]["streams"],
+                       "rollouts_per_stream": m["geometry"]["chunk"]},
             "rollout_steps_per_sec": value * depth,
-            "e2e": {"value": e2e, "unit": "rollouts/s", "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": n + 64 + 624 * 4, "rollout_steps_per_sec": e2e * depth},
-            "gpu_launches": int(launches),
-            "clocks": clocks,
-            "roofline": {"bound": "int_issue", "kernel": w["kernel"], "kernel_ms": k_ms,
-                         "kernel_share_of_step": k_ms / ms_step,
-                         "achieved": achieved / 1e9, "peak": int_peak / 1e9, "unit": "Gop/s",
-                         "frac": achieved / int_peak,
-                         "traffic": w.get("traffic") if n == (1 << 24) else None,
-                         "executed": {"ops_per_step": w["ops_exec"], "achieved": executed / 1e9,
-                                      "frac": executed / int_peak, "frac_of_alu_pipe": executed / int_peak_alu},
-                         "note": note,
-                         "hbm": {"achieved": hbm_bytes / (k_ms * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
-                                 "unit": "GB/s", "frac": hbm_bytes / (k_ms * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                                 "peak_source": peak_kind}},
-            "sums": {"row_wins": int(totals[0]), "draws": int(totals[1]), "row_losses": int(totals[2]),
-                     "steps": int(totals[3])},
+            "e2e": {"value": e2e, "unit": "rollouts/s", "h2d_bytes_per_step": m["h2d"], "d2h_bytes_per_step": m["d2h"],
+                    "rollout_steps_per_sec": e2e * depth},
+            "gpu_launches": m["launches"],
+            "clocks": m["clocks"],
+            "roofline": roofline(w, m, int_peak, int_peak_alu, peaks, peak_kind, workload_name),
+            "sums": {"row_wins": int(m["totals"][0]), "draws": int(m["totals"][1]), "row_losses": int(m["totals"][2]),
+                     "steps": int(m["totals"][3])},
+            "cold_call": dict(m["cold"], context_create_ms=rig.create_ms,
+                              note="first call of this batch shape in a fresh context (jump-polynomial family of a new "
+                                   "stride, state-stream table, buffers); pcu_warmup pays it ahead of time; not in "
+                                   "ms_per_step"),
         }
+        if packed_m:
+            pe = float(n) * world * packed_m["steps"] / (packed_m["e2e_ms"] * 1e-3)
+            line["e2e_packed2"] = {"value": pe, "unit": "rollouts/s", "d2h_bytes_per_step": packed_m["d2h"],
+                                   "note": "same call with pcu_out.payoff_packed2 (2 bits per rollout) instead of bytes"}
+        wl = {}
+        for name, (we, em, scaling, key) in extras.items():
+            tot = float(em["n"]) * world * em["steps"]
+            rf = roofline(we, em, int_peak, int_peak_alu, peaks, peak_kind, key)
+            wl[name] = {"workload": describe(we, em["n"]), "scaling": scaling, "rollouts_per_step_all_gpus": em["n"] * world,
+                        "value": tot / (em["dev_ms"] * 1e-3), "unit": "rollouts/s",
+                        "rollout_steps_per_sec": tot / (em["dev_ms"] * 1e-3) * we["depth"],
+                        "e2e": tot / (em["e2e_ms"] * 1e-3), "ms_per_step": em["dev_ms"] / em["steps"],
+                        "kernel_ms": em["kernel_ms"], "kernel_path": em["path"], "model_streams": em["geometry"]["streams"],
+                        "gpu_launches": em["launches"],
+                        "roofline": {"frac": rf["frac"], "executed": rf["executed"], "kernel": rf["kernel"]},
+                        "cold_first_call_ms": em["cold"]["first_call_ms"]}
+        if search is not None:
+            wl["search_offpolicy"] = search
+        if wl:
+            line["workloads"] = wl
+        if single is not None:
+            line["single_process_multi_gpu"] = single
         if world == 1 and not args.no_cpu:
             cb = cpu_reference_rate(w, seconds_target=12.0)
+            c1 = cpu_reference_rate(w, seconds_target=5.0, threads=1)
             line["cpu_baseline"] = {"value": cb["rate"], "unit": "rollouts/s", "cores": cb["cores"], "kind": cb["kind"],
-                                    "sample": f"{cb['n']} rollouts of the same workload in {cb['seconds']:.1f} s"}
+                                    "sample": f"{cb['n']} rollouts of the same workload in {cb['seconds']:.1f} s",
+                                    "one_thread": {"value": c1["rate"], "cores": 1,
+                                                   "sample": f"{c1['n']} rollouts in {c1['seconds']:.1f} s"}}
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.barrier()
-        dist.destroy_process_group()
-    ctx.close()
+    rig.close()
 
 
 def main():
@@ -484,6 +663,8 @@ def main():
     ap.add_argument("--streams-per-sm", type=int, default=0, help="model-stream generator warps per SM (default 4)")
     ap.add_argument("--no-zero-copy", action="store_true", help="e2e: stage payoffs in HBM and copy them back")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-extra", action="store_true", help="headline workload only (no `workloads` object): ncu runs")
+    ap.add_argument("--rb", type=int, default=0, help="rollouts per consumer batch of the fused kernel (32, 64, 128)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.workload == "search_offpolicy":
@@ -492,7 +673,7 @@ def main():
     if args.impl == "reference":
         run_reference_arm(args, w)
     else:
-        run_ours(args, w)
+        run_ours(args, w, args.workload)
 
 
 if __name__ == "__main__":

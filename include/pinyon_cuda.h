@@ -61,6 +61,8 @@ int pcu_create(int device_id, pcu_ctx **out);
  * NCCL is loaded at run time (libnccl.so.2); PCU_ERR_UNSUPPORTED if it is absent and n > 1.  Listing one GPU n
  * times is allowed (a test configuration: the shards then share the GPU and the counters are summed by a kernel). */
 int pcu_create_multi(const int *device_ids, int n, pcu_ctx **out);
+/* Number of CUDA devices of compute capability 10.x visible to this process (0 without a usable GPU). */
+int pcu_visible_devices(void);
 /* GPUs behind a context: 1 for pcu_create. */
 int pcu_device_count(const pcu_ctx *ctx);
 void pcu_destroy(pcu_ctx *ctx);

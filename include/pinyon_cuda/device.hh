@@ -8,6 +8,7 @@
 #pragma once
 
 #include <cstdint>
+#include <cstdlib>
 #include <memory>
 #include <mutex>
 #include <stdexcept>
@@ -83,12 +84,49 @@ class Device {
             throw Error(rc, "pcu_create(" + std::to_string(device_id) +
                                 ") failed: libpinyon_cuda needs an sm_100 GPU and has no CPU fallback");
     }
+    /* One context over several GPUs (pcu_create_multi): batched inference is sharded by rollout index inside the
+     * library and its counters are reduced with NCCL; single leaves and small batches stay on device_ids[0]. */
+    explicit Device(const std::vector<int> &device_ids) {
+        const int rc = pcu_create_multi(device_ids.data(), static_cast<int>(device_ids.size()), &ctx);
+        if (rc != PCU_OK)
+            throw Error(rc, "pcu_create_multi over " + std::to_string(device_ids.size()) +
+                                " GPUs failed: libpinyon_cuda needs sm_100 GPUs (and NCCL for more than one); "
+                                "there is no CPU fallback");
+    }
     Device(const Device &) = delete;
     Device &operator=(const Device &) = delete;
     ~Device() { pcu_destroy(ctx); }
 
     void check(int rc) const {
         if (rc != PCU_OK) throw Error(rc, std::string("libpinyon_cuda: ") + pcu_last_error(ctx));
+    }
+
+    /* Process-wide context over EVERY visible sm_100 GPU (what `Types::Model model{prng{0}}` gets), created on first
+     * use.  PINYON_CUDA_DEVICES="0,2,3" restricts the set. */
+    static std::shared_ptr<Device> shared_all() {
+        static std::mutex mu;
+        static std::weak_ptr<Device> cache;
+        std::lock_guard<std::mutex> lock(mu);
+        std::shared_ptr<Device> d = cache.lock();
+        if (!d) {
+            std::vector<int> ids;
+            if (const char *env = std::getenv("PINYON_CUDA_DEVICES")) {
+                for (const char *p = env; *p;) {
+                    char *end = nullptr;
+                    const long v = std::strtol(p, &end, 10);
+                    if (end == p) break;
+                    ids.push_back(static_cast<int>(v));
+                    p = (*end == ',') ? end + 1 : end;
+                }
+            } else {
+                const int n = pcu_visible_devices();
+                for (int i = 0; i < n; ++i) ids.push_back(i);
+            }
+            if (ids.empty()) ids.push_back(0); /* no usable GPU: let pcu_create report it */
+            d = ids.size() == 1 ? std::make_shared<Device>(ids[0]) : std::make_shared<Device>(ids);
+            cache = d;
+        }
+        return d;
     }
 
     /* Process-wide context per GPU, created on first use. */

@@ -57,7 +57,8 @@ struct MonteCarloModel : Types {
         typename Types::PRNG device;
         std::shared_ptr<Device> gpu; /* shared by copies: models are copied per thread */
 
-        Model(const typename Types::PRNG &device) : device{device}, gpu{Device::shared(0)} {}
+        /* every visible GPU: batched inference shards over them inside the library (pcu_create_multi) */
+        Model(const typename Types::PRNG &device) : device{device}, gpu{Device::shared_all()} {}
         Model(const typename Types::PRNG &device, std::shared_ptr<Device> gpu) : device{device}, gpu{std::move(gpu)} {}
 
         /* 2 * row payoff -> Types::Value exactly as random-tree.hh:99-103 builds it */

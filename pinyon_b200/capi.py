@@ -39,7 +39,7 @@ EXPORTS = [
     "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches", "pcu_last_kernel_ms",
     "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next", "pcu_mt_discard_family",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
-    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup",
+    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup", "pcu_visible_devices",
 ]
 
 
@@ -121,6 +121,7 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_create_multi.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(vp)]
     lib.pcu_create_multi.restype = C.c_int
     lib.pcu_device_count.argtypes = [vp]
+    lib.pcu_visible_devices.restype = C.c_int
     lib.pcu_get_stat.argtypes = [vp, C.c_char_p, C.POINTER(C.c_double)]
     lib.pcu_warmup.argtypes = [vp, u64, u32]
     _lib = lib

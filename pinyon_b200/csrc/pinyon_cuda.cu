@@ -1909,6 +1909,20 @@ int pcu_create_multi(const int *device_ids, int n, pcu_ctx **out) {
     return PCU_OK;
 }
 
+int pcu_visible_devices(void) {
+    int count = 0, ok = 0;
+    if (cudaGetDeviceCount(&count) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    for (int i = 0; i < count; ++i) {
+        int major = 0;
+        if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, i) == cudaSuccess && major == 10) ++ok;
+        else break; /* device ids must stay contiguous from 0 */
+    }
+    return ok;
+}
+
 int pcu_device_count(const pcu_ctx *ctx) { return !ctx ? 0 : ctx->multi ? (int)ctx->multi->kids.size() : 1; }
 
 int pcu_get_stat(pcu_ctx *ctx, const char *key, double *value) {

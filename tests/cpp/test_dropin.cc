@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstring>
 #include <memory>
+#include <string>
 #include <thread>
 #include <unordered_map>
 #include <vector>
@@ -340,7 +341,56 @@ static void test_threaded_copies() {
     std::printf("threaded copies ok\n");
 }
 
+// ONE model.inference(batch_in, batch_out) on a context that spans several GPUs (pcu_create_multi: contiguous
+// rollout-index shards, per-shard slices of the one model stream, NCCL all-reduce of the counters) must equal the same
+// call on one GPU byte for byte, including model.device afterwards (monte-carlo-model.hh:58-67).  With one GPU in the box
+// the shards share it (device 0 listed three times), which runs the same plan, offsets and engine hand-back.
+static void test_multi_gpu_batch(size_t n) {
+    std::vector<int> ids;
+    const int visible = pcu_visible_devices();
+    if (visible >= 2)
+        for (int i = 0; i < visible; ++i) ids.push_back(i);
+    else
+        ids = {0, 0, 0};
+    auto multi = std::make_shared<PinyonCuda::Device>(ids);
+    GpuTree::Model one{prng{3}, PinyonCuda::Device::shared(0)}, many{prng{3}, multi};
+    const RandomTree<>::State root{prng{0}, 10, 3, 3, 1};
+    GpuTree::ModelBatchInput in_one{};
+    for (size_t i = 0; i < n; ++i) one.add_to_batch_input(RandomTree<>::State{root}, in_one);
+    GpuTree::ModelBatchInput in_many = in_one;
+    GpuTree::ModelBatchOutput out_one{}, out_many{};
+    one.inference(in_one, out_one);
+    many.inference(in_many, out_many);
+    CHECK(std::string(pcu_last_path(multi->ctx)).find(" x") != std::string::npos);
+    CHECK(pcu_device_count(multi->ctx) == int(ids.size()));
+    CHECK(out_one.payoff_x2.size() == n && out_one.payoff_x2 == out_many.payoff_x2);
+    for (int k = 0; k < 8; ++k) CHECK(out_one.sums[k] == out_many.sums[k]);
+    CHECK(out_one.sums[0] + out_one.sums[1] + out_one.sums[2] == n);
+    CHECK(one.device.uniform_64() == many.device.uniform_64());
+    // and the head of the batch against the reference model itself
+    RefTree::Model ref{prng{3}};
+    for (int i = 0; i < 3000; ++i) {
+        RefTree::ModelOutput a;
+        GpuTree::ModelOutput b;
+        ref.inference(RandomTree<>::State{root}, a);
+        many.get_output(b, out_many, i);
+        CHECK(same_value(a.value, b.value));
+    }
+    std::printf("multi-GPU batch ok: %zu leaves over %zu shards (%d visible GPUs), path %s\n", n, ids.size(), visible,
+                pcu_last_path(multi->ctx));
+}
+
 int main(int argc, char **argv) {
+    if (argc > 2 && !std::strcmp(argv[1], "--multi")) {
+        try {
+            test_multi_gpu_batch(std::strtoull(argv[2], nullptr, 10));
+        } catch (const std::exception &e) {
+            std::printf("FAIL exception: %s\n", e.what());
+            ++g_failures;
+        }
+        std::printf(g_failures ? "FAILED (%d)\n" : "ALL OK\n", g_failures);
+        return g_failures ? 1 : 0;
+    }
     const bool gpu = argc > 1 && !std::strcmp(argv[1], "--gpu");
     test_engine_access();
     test_stream_locator();

@@ -21,8 +21,8 @@ def _binary():
     pytest.skip("test_dropin was not prebuilt and the reference headers are absent")
 
 
-def _run(flag):
-    res = subprocess.run([str(_binary()), flag], capture_output=True, text=True, timeout=600)
+def _run(*flags):
+    res = subprocess.run([str(_binary()), *flags], capture_output=True, text=True, timeout=900)
     print(res.stdout)
     print(res.stderr, file=sys.stderr)
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
@@ -46,6 +46,18 @@ def test_dropin_matches_reference_on_gpu():
     out = _run("--gpu")
     for part in ("single inference ok", "batch inference ok", "TreeBandit<Exp3>", "OffPolicy<Exp3>", "threaded copies ok"):
         assert part in out
+
+
+@pytest.mark.gpu
+def test_dropin_multi_gpu_batch_equals_single():
+    """One model.inference(batch_in, batch_out) on a multi-GPU context (pcu_create_multi) == the same call on one GPU,
+    byte for byte, including model.device afterwards: 2^24 leaves when the box has several GPUs, 2^22 shards sharing the
+    one GPU otherwise."""
+    import torch
+
+    n = 1 << (24 if torch.cuda.device_count() >= 2 else 22)
+    out = _run("--multi", str(n))
+    assert "multi-GPU batch ok" in out
 
 
 @pytest.mark.gpu
