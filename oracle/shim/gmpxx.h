@@ -35,6 +35,7 @@ class mpz_class {
     mpz_class(int v) { z_[0].v = v; }
     mpz_class(unsigned long v) { z_[0].v = static_cast<long>(v); }
     mpz_class(double v) { z_[0].v = static_cast<long>(v); }
+    mpz_class(const pinyon_shim_mpz_struct *z) { z_[0].v = z->v; } /* from an mpz_t, as libpinyon/lrslib.hh:157 does */
     long get_si() const { return z_[0].v; }
     double get_d() const { return static_cast<double>(z_[0].v); }
     std::string get_str() const { return std::to_string(z_[0].v); }

@@ -81,3 +81,39 @@ def test_search_bench_binary_ref_equals_gpu():
     for key in ("nodes", "visits", "value_total_row", "row_visits", "col_visits"):
         assert outs[0][key] == outs[1][key], key
     assert outs[0]["nodes"] == 3 * 4096
+
+
+def _callers_binary():
+    from pinyon_b200 import build_library
+
+    build_library()
+    if cpp_build.reference_available():
+        return cpp_build.build_callers()
+    if cpp_build.CALLERS_BIN.exists():
+        return cpp_build.CALLERS_BIN
+    pytest.skip("test_callers was not prebuilt and the reference headers are absent")
+
+
+def _run_callers(flag):
+    res = subprocess.run([str(_callers_binary()), flag], capture_output=True, text=True, timeout=900)
+    print(res.stdout)
+    print(res.stderr, file=sys.stderr)
+    assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-2000:]
+    assert "ALL OK" in res.stdout
+    return res.stdout
+
+
+def test_callers_concepts_and_stand_ins():
+    """tests/cpp/test_callers.cc compiles: IsBanditAlgorithmTypes<MatrixUCBFixed<Gpu>>, IsSearchTypes<TreeBandit<MatrixUCB
+    <Gpu>>> and FullTraversal's constraints hold over the GPU model; the lrslib stand-in and the MatrixUCB fix-up run the
+    reference's FullTraversal / MatrixUCB / TreeBanditFlat over the reference model on the host."""
+    out = _run_callers("--cpu")
+    assert "FullTraversal value" in out
+
+
+@pytest.mark.gpu
+def test_matrix_ucb_full_traversal_and_flat_over_gpu_model():
+    """SURVEY 8(f)3 + tests/flat.cc: FullTraversal (model.inference at the depth cut-off, LRSNash::solve per node),
+    TreeBandit<MatrixUCB> and TreeBandit vs TreeBanditFlat give identical results over the GPU model and the reference's."""
+    out = _run_callers("--gpu")
+    assert "TreeBandit<MatrixUCB>" in out and "flat equivalence" in out and out.count("FullTraversal seed") == 3
