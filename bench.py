@@ -194,13 +194,13 @@ def run_reference_arm(args, w):
 SEARCH_BIN = ROOT / "tests" / "cpp" / "_bin" / "bench_search"
 
 
-def run_search_binary(impl, gpu_id, seed, leaves, iters, warmup):
+def run_search_binary(impl, gpu_id, seed, leaves, iters, warmup, *extra):
     """tests/cpp/bench_search.cc: the reference's unmodified OffPolicy<Exp3<...>> over the reference model
     (impl 'ref') or the drop-in GPU model (impl 'gpu'); prebuilt next to the reference headers."""
     if not SEARCH_BIN.exists():
         raise RuntimeError(f"{SEARCH_BIN} missing: build it with `python tests/cpp/build.py` next to the reference")
-    res = subprocess.run([str(SEARCH_BIN), impl, str(gpu_id), str(seed), str(leaves), str(iters), str(warmup)],
-                         capture_output=True, text=True, timeout=1200)
+    res = subprocess.run([str(SEARCH_BIN), impl, str(gpu_id), str(seed), str(leaves), str(iters), str(warmup),
+                          *map(str, extra)], capture_output=True, text=True, timeout=1200)
     if res.returncode != 0:
         raise RuntimeError(f"bench_search {impl} failed: {res.stderr[-2000:]}")
     return json.loads(res.stdout.strip().splitlines()[-1])
@@ -576,6 +576,35 @@ def run_ours(args, w, workload_name):
                 search["reference_single_thread_leaves_per_s"] = ref["leaves_per_s"]
         except Exception as exc:  # the search line is extra evidence; the headline must still print
             search = {"error": str(exc)[:300]}
+    batched = None
+    if not args.no_extra and SEARCH_BIN.exists():
+        # BASELINE configs[4] as written: TreeBandit<Exp3> with GPU batched leaf evaluation, 4096 leaves per batch,
+        # root-parallel.  UNMODIFIED TreeBandit searches run in fibers on this rank's share of the host threads; their
+        # single-leaf inferences rendezvous in the batching adapter (include/pinyon_cuda/batcher.hh).
+        try:
+            cores = max(1, (os.cpu_count() or 1) // world)
+            fibers = max(1, (3 * 4096 + cores - 1) // cores)  # three batches in flight per GPU
+            iters = 150
+            rig.barrier()
+            mine = run_search_binary("gpu_tb_batched", rig.local, 1000003 * rank, 4096, iters, 0, cores, fibers)
+            sec = rig.reduce([mine["seconds"]], "max")[0]
+            tot = rig.reduce([mine["trees"] * iters, mine["gpu_calls"], mine["gpu_leaves"]], "sum")
+            batched = {"metric": "search leaves/sec", "value": tot[0] / sec, "unit": "leaves/s",
+                       "config": "TreeBandit<Exp3<BatchedMonteCarloModel<RandomTree 3x3x1 d10>>> unmodified, root-parallel: "
+                                 f"{mine['trees']} trees per GPU in fibers on {cores} host threads, {iters} iterations each, "
+                                 "4096 leaves per GPU call (model-rng mode W)",
+                       "host_threads_per_gpu": cores, "trees_per_gpu": mine["trees"], "gpu_calls": tot[1],
+                       "leaves_per_gpu_call": tot[2] / max(1, tot[1]), "seconds": sec}
+            if rank == 0:
+                ref1 = run_search_binary("ref_tb", 0, 0, 0, 20000, 2000)
+                refm = run_search_binary("ref_tb_mt", 0, 0, 0, iters, 0, os.cpu_count() or 1, 64)
+                batched["reference_tree_bandit_one_thread_leaves_per_s"] = ref1["leaves_per_s"]
+                batched["reference_tree_bandit_all_threads_leaves_per_s"] = refm["leaves_per_s"]
+                batched["reference_threads"] = refm["threads"]
+                batched["vs_reference_one_thread"] = batched["value"] / ref1["leaves_per_s"]
+                batched["vs_reference_all_threads"] = batched["value"] / refm["leaves_per_s"]
+        except Exception as exc:
+            batched = {"error": str(exc)[:300]}
 
     single = None
     if world > 1 and not args.no_extra:
@@ -637,6 +666,8 @@ def run_ours(args, w, workload_name):
                         "cold_first_call_ms": em["cold"]["first_call_ms"]}
         if search is not None:
             wl["search_offpolicy"] = search
+        if batched is not None:
+            wl["search_treebandit_batched"] = batched
         if wl:
             line["workloads"] = wl
         if single is not None:

@@ -104,15 +104,24 @@ void pcu_host_free(pcu_ctx *ctx, void *p);
  * with a CPU model that ran the same batch.
  *
  * PCU_MODEL_PER_ROLLOUT ("mode P"): rollout i runs on a fresh prng{seeds[i]}; what the
- * reference computes when called as Model{prng{seeds[i]}}.inference(state_i). */
+ * reference computes when called as Model{prng{seeds[i]}}.inference(state_i).
+ *
+ * PCU_MODEL_WORDS ("mode W"): every rollout brings the engine words its own model would draw: words[] holds, rollout
+ * after rollout, the next 4 * depth_i RAW (untempered) std::mt19937 state words of that rollout's engine (two
+ * random_int per step, two words each, monte-carlo-model.hh:89-90).  This is how single-leaf inferences of MANY
+ * models (one per search tree, each with its own sequential stream; tree-bandit.hh:103,111) are evaluated as one
+ * batch: the caller takes the words with pcu_mt_take_raw, which advances its engine exactly as the rollout would;
+ * tempering, the uniform_int arithmetic (random.hh:26,28) and the rollout run on the GPU. */
 #define PCU_MODEL_STREAM 0
 #define PCU_MODEL_PER_ROLLOUT 1
+#define PCU_MODEL_WORDS 2
 
 typedef struct {
     int32_t mode;
     uint32_t *mt_x;        /* mode S: [624] engine words, HOST memory, updated in place */
     uint32_t *mt_p;        /* mode S: next-word position 0..624, HOST memory, updated in place */
     const uint64_t *seeds; /* mode P: [n] seeds, in the memory space of the batch */
+    const uint32_t *words; /* mode W: [4 * sum of depths] raw engine words, in the memory space of the batch */
 } pcu_model_rng;
 
 /* Host-side engine helpers (no GPU needed).  pcu_mt_seed == std::mt19937::seed as
@@ -121,6 +130,9 @@ typedef struct {
 void pcu_mt_seed(uint64_t seed, uint32_t *mt_x, uint32_t *mt_p);
 int pcu_mt_discard(uint32_t *mt_x, uint32_t *mt_p, uint64_t n);
 uint32_t pcu_mt_next(uint32_t *mt_x, uint32_t *mt_p);
+/* The next n RAW (untempered) state words of the engine, which is advanced by n draws: the words a mode-W rollout of
+ * n / 4 steps consumes.  pcu_mt_next(...) == temper(raw word). */
+int pcu_mt_take_raw(uint32_t *mt_x, uint32_t *mt_p, uint64_t n, uint32_t *out);
 /* Diagnostic: the engine advanced by c * stride draws through the cached polynomial family
  * x^(c * stride) mod phi that the device jump-ahead uses for its checkpoints (c < 65536). */
 int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint64_t c);

@@ -7,6 +7,7 @@
 // serialises model copies that share it.
 #pragma once
 
+#include <array>
 #include <cstdint>
 #include <cstdlib>
 #include <memory>
@@ -35,9 +36,12 @@ class StreamLocator {
     struct PerSeed {
         std::vector<uint32_t> x;                    /* current block of the generator */
         std::vector<std::array<uint32_t, 3>> heads; /* heads[k] = (x[0], x[1], x[623]) after k refills */
+        size_t last = 0;                            /* block of the previous hit: searches revisit the same few blocks */
     };
     std::unordered_map<uint32_t, PerSeed> seeds_;
     static constexpr size_t MAX_BLOCKS = size_t(1) << 16; /* 40.9 M draws */
+    static constexpr size_t MAX_SEEDS = 256; /* cache bound: a batch of distinct roots must not keep 2.5 KB per root
+                                              * forever (a seed seen again after eviction is re-seeded: 623 steps) */
 
     static void refill(std::vector<uint32_t> &x) {
         for (uint32_t k = 0; k < MT_WORDS; ++k) {
@@ -49,6 +53,7 @@ class StreamLocator {
    public:
     /* Draws made since seeding, or UINT64_MAX if the engine is not on prng{seed}'s stream. */
     uint64_t locate(uint64_t seed, const EngineImage &img) {
+        if (seeds_.size() >= MAX_SEEDS && !seeds_.count(static_cast<uint32_t>(seed))) seeds_.clear();
         PerSeed &s = seeds_[static_cast<uint32_t>(seed)];
         if (s.x.empty()) {
             s.x.resize(MT_WORDS);
@@ -57,16 +62,22 @@ class StreamLocator {
             s.heads.push_back({s.x[0], s.x[1], s.x[MT_WORDS - 1]});
         }
         const std::array<uint32_t, 3> want{img.x[0], img.x[1], img.x[MT_WORDS - 1]};
-        for (size_t k = 0;; ++k) {
-            if (k == s.heads.size()) {
-                if (k >= MAX_BLOCKS) return UINT64_MAX;
-                refill(s.x);
-                s.heads.push_back({s.x[0], s.x[1], s.x[MT_WORDS - 1]});
-            }
-            if (s.heads[k] == want) {
-                if (k == 0) return img.p == MT_WORDS ? 0 : UINT64_MAX; /* a seeded engine has drawn nothing */
-                return uint64_t(MT_WORDS) * (k - 1) + img.p;
-            }
+        auto hit = [&](size_t k) -> uint64_t {
+            s.last = k;
+            if (k == 0) return img.p == MT_WORDS ? 0 : UINT64_MAX; /* a seeded engine has drawn nothing */
+            return uint64_t(MT_WORDS) * (k - 1) + img.p;
+        };
+        /* the blocks already generated, starting where the last query ended and wrapping once */
+        const size_t have = s.heads.size();
+        for (size_t i = 0; i < have; ++i) {
+            const size_t k = (s.last + i) % have;
+            if (s.heads[k] == want) return hit(k);
+        }
+        for (size_t k = have;; ++k) { /* further along the stream than ever before: generate on */
+            if (k >= MAX_BLOCKS) return UINT64_MAX;
+            refill(s.x);
+            s.heads.push_back({s.x[0], s.x[1], s.x[MT_WORDS - 1]});
+            if (s.heads[k] == want) return hit(k);
         }
     }
 };

@@ -176,7 +176,7 @@ struct MonteCarloModel : Types {
             }
         }
 
-       private:
+       protected: /* shared with BatchedMonteCarloModel (batcher.hh) */
         template <typename F>
         void with_engine(F &&call) {
             using Access = EngineAccess<typename Types::PRNG>;

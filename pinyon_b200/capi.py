@@ -24,6 +24,7 @@ PCU_MEM_HOST = 0
 PCU_MEM_DEVICE = 1
 PCU_MODEL_STREAM = 0
 PCU_MODEL_PER_ROLLOUT = 1
+PCU_MODEL_WORDS = 2
 
 HASH_INIT = 2166136261
 HASH_MUL = 16777619
@@ -39,12 +40,13 @@ EXPORTS = [
     "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches", "pcu_last_kernel_ms",
     "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next", "pcu_mt_discard_family",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
-    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup", "pcu_visible_devices",
+    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup", "pcu_visible_devices", "pcu_mt_take_raw",
 ]
 
 
 class ModelRng(C.Structure):
-    _fields_ = [("mode", C.c_int32), ("mt_x", C.c_void_p), ("mt_p", C.c_void_p), ("seeds", C.c_void_p)]
+    _fields_ = [("mode", C.c_int32), ("mt_x", C.c_void_p), ("mt_p", C.c_void_p), ("seeds", C.c_void_p),
+                ("words", C.c_void_p)]
 
 
 class RtBatch(C.Structure):
@@ -113,6 +115,7 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_mt_seed.restype = None
     lib.pcu_mt_discard.argtypes = [vp, vp, u64]
     lib.pcu_mt_discard_family.argtypes = [vp, vp, u64, u64]
+    lib.pcu_mt_take_raw.argtypes = [vp, vp, u64, vp]
     lib.pcu_mt_next.argtypes = [vp, vp]
     lib.pcu_mt_next.restype = u32
     lib.pcu_rollout_random_tree.argtypes = [vp, C.POINTER(RtBatch), C.POINTER(ModelRng), C.POINTER(Out)]
@@ -150,6 +153,14 @@ class Engine:
 
     def next(self) -> int:
         return load_library().pcu_mt_next(self.x.ctypes.data, self.p.ctypes.data)
+
+    def take_raw(self, n: int) -> np.ndarray:
+        """The next n RAW state words (pcu_mt_take_raw): what a mode-W rollout of n / 4 steps consumes."""
+        out = np.zeros(n, np.uint32)
+        rc = load_library().pcu_mt_take_raw(self.x.ctypes.data, self.p.ctypes.data, n, out.ctypes.data)
+        if rc:
+            raise PcuError(rc, "pcu_mt_take_raw")
+        return out
 
     def copy(self) -> "Engine":
         e = Engine.__new__(Engine)
@@ -260,9 +271,12 @@ class Context:
         return arr
 
     # -- the hot path ---------------------------------------------------------------
-    def _rng(self, engine, model_seeds):
+    def _rng(self, engine, model_seeds, model_words=None):
         r = ModelRng()
-        if model_seeds is not None:
+        if model_words is not None:
+            r.mode = PCU_MODEL_WORDS
+            r.words = _ptr(model_words)
+        elif model_seeds is not None:
             r.mode = PCU_MODEL_PER_ROLLOUT
             r.seeds = _ptr(model_seeds)
         else:
@@ -288,7 +302,7 @@ class Context:
     def rollout_random_tree(self, n, *, rows, cols, transitions=1, thr=(0, 1), depth=None, state_seed=0,
                             state_pos=None, transition_seed=0, payoff_bias=0, engine: Engine = None,
                             model_seeds=None, payoff=None, traj=None, traj_stride=0, traj_hash=None, sums=None,
-                            payoff_packed=None):
+                            payoff_packed=None, model_words=None):
         """pcu_rollout_random_tree.  Scalar arguments are batch-uniform; numpy arrays
         (host) or torch CUDA tensors (device) are per-rollout.  state_pos defaults to a
         freshly constructed root: 2*rows*cols*transitions draws."""
@@ -315,14 +329,14 @@ class Context:
         put("payoff_bias", payoff_bias, np.int32)
         b.rows, b.cols, b.transitions = rows, cols, transitions
         b.thr_p, b.thr_q = thr
-        device = _is_device(*arrays, model_seeds, payoff, traj, traj_hash, sums, payoff_packed)
+        device = _is_device(*arrays, model_seeds, model_words, payoff, traj, traj_hash, sums, payoff_packed)
         b.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
-        r = self._rng(engine, model_seeds)
+        r = self._rng(engine, model_seeds, model_words)
         o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_random_tree(self.h, C.byref(b), C.byref(r), C.byref(o)))
 
     def rollout_mold(self, n, *, n_actions, depth, engine: Engine = None, model_seeds=None, payoff=None, traj=None,
-                     traj_stride=0, traj_hash=None, sums=None, payoff_packed=None):
+                     traj_stride=0, traj_hash=None, sums=None, payoff_packed=None, model_words=None):
         b = MoldBatch()
         b.n = n
         arrays = []
@@ -333,8 +347,8 @@ class Context:
             arrays.append(depth)
             b.depth = _ptr(depth)
         b.n_actions = n_actions
-        device = _is_device(*arrays, model_seeds, payoff, traj, traj_hash, sums, payoff_packed)
+        device = _is_device(*arrays, model_seeds, model_words, payoff, traj, traj_hash, sums, payoff_packed)
         b.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
-        r = self._rng(engine, model_seeds)
+        r = self._rng(engine, model_seeds, model_words)
         o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_mold(self.h, C.byref(b), C.byref(r), C.byref(o)))

@@ -71,6 +71,7 @@ struct pcu_ctx {
         size_t bytes;
     };
     std::vector<PendingCopy> pending_in; /* stage_in copies not yet enqueued (see inputs_ready) */
+    std::vector<uint64_t> host_step_off;  /* mode W, ragged host batches: first step of every rollout */
     bool ev_valid = false;
     std::string err;
     std::string path;
@@ -1005,6 +1006,9 @@ int check_common(pcu_ctx *ctx, const void *batch, const pcu_model_rng *rng, cons
         if (*rng->mt_p > MT_N) return fail(ctx, PCU_ERR_INVALID, "mt_p %u out of range", *rng->mt_p);
     } else if (rng->mode == PCU_MODEL_PER_ROLLOUT) {
         if (!rng->seeds) return fail(ctx, PCU_ERR_INVALID, "mode P needs seeds");
+    } else if (rng->mode == PCU_MODEL_WORDS) {
+        if (!rng->words) return fail(ctx, PCU_ERR_INVALID, "mode W needs words");
+        if ((uintptr_t)rng->words % 4) return fail(ctx, PCU_ERR_INVALID, "mode W words must be 4-byte aligned");
     } else {
         return fail(ctx, PCU_ERR_INVALID, "unknown model rng mode %d", rng->mode);
     }
@@ -1217,6 +1221,23 @@ uint32_t pcu_mt_next(uint32_t *mt_x, uint32_t *mt_p) {
     return mt_temper(mt_x[(*mt_p)++]);
 }
 
+int pcu_mt_take_raw(uint32_t *mt_x, uint32_t *mt_p, uint64_t n, uint32_t *out) {
+    if (!mt_x || !mt_p || *mt_p > MT_N || (n && !out)) return PCU_ERR_INVALID;
+    while (n) {
+        if (*mt_p >= MT_N) {
+            host_mt_refill(mt_x);
+            *mt_p = 0;
+        }
+        uint64_t take = MT_N - *mt_p;
+        if (take > n) take = n;
+        memcpy(out, mt_x + *mt_p, sizeof(uint32_t) * take);
+        out += take;
+        *mt_p += (uint32_t)take;
+        n -= take;
+    }
+    return PCU_OK;
+}
+
 int pcu_mt_discard(uint32_t *mt_x, uint32_t *mt_p, uint64_t n) {
     if (!mt_x || !mt_p || *mt_p > MT_N) return PCU_ERR_INVALID;
     if (n < (1ull << 22)) {
@@ -1251,6 +1272,84 @@ int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint6
 }  // extern "C"
 
 namespace {
+
+/* Mode W: the batch's raw model words on the device (16-byte aligned for the kernels' uint4 loads) and, for ragged
+ * depths, the first step of every rollout.  Host batches: the prefix sum is a host loop over depths the caller holds
+ * anyway, uploaded with the words.  Device batches: the scan kernels. */
+struct WordsDev {
+    const uint32_t *words = nullptr;
+    const uint64_t *step_off = nullptr;
+    uint64_t total_steps = 0;
+    uint32_t dmax = 0;
+};
+
+int stage_words(pcu_ctx *ctx, int mem, uint64_t n, const uint16_t *h_depth, const uint16_t *d_depth, uint32_t depth_u,
+                const pcu_model_rng *rng, WordsDev &wd) {
+    if (mem == PCU_MEM_HOST) {
+        wd.dmax = depth_u;
+        wd.total_steps = n * (uint64_t)depth_u;
+        if (h_depth) {
+            CU(ctx->buf[B_STEPOFF].ensure(sizeof(uint64_t) * (n + 1)));
+            std::vector<uint64_t> &off = ctx->host_step_off;
+            off.resize(n + 1);
+            uint64_t acc = 0;
+            uint32_t dm = 0;
+            for (uint64_t i = 0; i < n; ++i) {
+                off[i] = acc;
+                acc += h_depth[i];
+                dm = std::max<uint32_t>(dm, h_depth[i]);
+            }
+            off[n] = acc;
+            wd.total_steps = acc;
+            wd.dmax = dm;
+            ctx->pending_in.push_back({ctx->buf[B_STEPOFF].p, off.data(), sizeof(uint64_t) * (n + 1)});
+            wd.step_off = reinterpret_cast<const uint64_t *>(ctx->buf[B_STEPOFF].p);
+        }
+        CU(ctx->buf[B_WORDS].ensure(sizeof(uint32_t) * 4 * wd.total_steps + 16));
+        if (wd.total_steps)
+            ctx->pending_in.push_back({ctx->buf[B_WORDS].p, rng->words, sizeof(uint32_t) * 4 * wd.total_steps});
+        wd.words = reinterpret_cast<const uint32_t *>(ctx->buf[B_WORDS].p);
+        return PCU_OK;
+    }
+    if ((uintptr_t)rng->words % 16) return fail(ctx, PCU_ERR_INVALID, "mode W words in device memory must be 16-byte aligned");
+    wd.words = rng->words;
+    wd.dmax = depth_u;
+    wd.total_steps = n * (uint64_t)depth_u;
+    if (d_depth) {
+        int rc = scan_depths(ctx, d_depth, n, &wd.step_off, &wd.total_steps);
+        if (rc) return rc;
+        wd.dmax = 0; /* unknown on the host: the table path is not taken */
+    }
+    return PCU_OK;
+}
+
+int words_to_codes(pcu_ctx *ctx, const WordsDev &wd, uint32_t rows, uint32_t cols, bool *code16) {
+    const bool c16 = (uint64_t)rows * cols > 256;
+    *code16 = c16;
+    CU(ctx->buf[B_CODES].ensure((wd.total_steps + 8) * (c16 ? 2 : 1)));
+    if (!wd.total_steps) return PCU_OK;
+    const unsigned blocks = (unsigned)((wd.total_steps + 255) / 256);
+    const FoldConst mrow = make_fold_const(rows), mcol = make_fold_const(cols);
+    if (c16)
+        k_words_to_codes<uint16_t><<<blocks, 256, 0, ctx->stream>>>(wd.words, wd.total_steps, cols, mrow, mcol,
+                                                                     reinterpret_cast<uint16_t *>(ctx->buf[B_CODES].p));
+    else
+        k_words_to_codes<uint8_t><<<blocks, 256, 0, ctx->stream>>>(wd.words, wd.total_steps, cols, mrow, mcol,
+                                                                    reinterpret_cast<uint8_t *>(ctx->buf[B_CODES].p));
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
+
+int launch_leaf(pcu_ctx *ctx, const LeafParams &L) {
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    k_leaf_table<<<(unsigned)((L.n + 127) / 128), 128, 0, ctx->stream>>>(L);
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
 
 /* One GPU's share of the work: everything below runs on ctx->device. */
 int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
@@ -1321,6 +1420,10 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+    WordsDev wd;
+    if (rng->mode == PCU_MODEL_WORDS && (rc = stage_words(ctx, b->mem, n, b->mem == PCU_MEM_HOST ? b->depth : nullptr,
+                                                          d_depth, b->depth_u, rng, wd)))
+        return rc;
     /* mode S with uniform depth: the action-code generator needs none of the batch arrays, so the copies above are
      * enqueued behind it and run beside it on the copy stream */
     const bool defer_inputs = rng->mode == PCU_MODEL_STREAM && !b->depth && b->mem == PCU_MEM_HOST;
@@ -1330,10 +1433,13 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
     uint32_t fq_w = 0;
     if (T > 1 && (rc = upload_fq(ctx, T, &d_fq, &fq_w))) return rc;
 
-    /* ---- fused path: mode S, uniform depth, one shared state stream, host-visible positions */
-    bool fused = !ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && !b->state_seed &&
-                 (T == 1 || !b->transition_seed) && (!b->state_pos || b->mem == PCU_MEM_HOST) &&
-                 stream_fits(b->depth_u, (uint64_t)b->rows * b->cols);
+    /* ---- table paths: one shared state stream, host-visible positions.  Mode S with uniform depth: the fused
+     * generator + consumer kernel; mode W (leaf batches of many searches from one root): k_leaf_table */
+    const bool leaf = rng->mode == PCU_MODEL_WORDS && (!b->depth || wd.dmax > 0);
+    const uint32_t table_depth = leaf ? wd.dmax : b->depth_u;
+    bool fused = !ctx->force_general && !b->state_seed && (T == 1 || !b->transition_seed) &&
+                 (!b->state_pos || b->mem == PCU_MEM_HOST) &&
+                 (leaf || (rng->mode == PCU_MODEL_STREAM && !b->depth && stream_fits(b->depth_u, (uint64_t)b->rows * b->cols)));
     uint32_t pos_min = b->state_pos_u, pos_max = b->state_pos_u;
     if (fused && b->state_pos) {
         pos_min = 0xffffffffu;
@@ -1347,7 +1453,7 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
     uint64_t span = 0;
     if (fused) {
         const uint64_t per_step = (uint64_t)b->rows * b->cols * T + 2 + gen_words;
-        span = (uint64_t)(pos_max - pos_min) + gen_words + per_step * b->depth_u + 8;
+        span = (uint64_t)(pos_max - pos_min) + gen_words + per_step * table_depth + 8;
         if (span > (1u << 22)) fused = false;
     }
     if (fused) {
@@ -1387,6 +1493,37 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
             key.thr_p = b->thr_p;
             key.thr_q = b->thr_q;
             ctx->last_table_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        }
+        if (leaf) {
+            LeafParams L;
+            memset(&L, 0, sizeof(L));
+            L.n = n;
+            L.kind = KIND_TREE;
+            L.cols = b->cols;
+            L.T = T;
+            L.gen_words = gen_words;
+            L.mrow = make_fold_const(b->rows);
+            L.mcol = make_fold_const(b->cols);
+            L.words = wd.words;
+            L.step_off = wd.step_off;
+            L.depth = d_depth;
+            L.depth_u = b->depth_u;
+            L.tab = reinterpret_cast<const uint8_t *>(ctx->buf[B_TAB].p);
+            L.tab_base = tab_base;
+            L.tab_len = tab_len;
+            L.state_pos = d_pos;
+            L.state_pos_u = b->state_pos_u;
+            L.bias = d_bias;
+            L.bias_u = b->payoff_bias_u;
+            if ((rc = pack_source(ctx, od, n, &L.payoff))) return rc;
+            L.traj = od.traj;
+            L.traj_stride = out->traj_stride;
+            L.traj_hash = od.hash;
+            L.sums = od.sums;
+            ctx->path = "leaf_table_W";
+            if ((rc = launch_leaf(ctx, L))) return rc;
+            if ((rc = pack_after(ctx, od, n, L.payoff))) return rc;
+            return finish_all(ctx, out, n, od, rng);
         }
         Stream2Params P;
         memset(&P, 0, sizeof(P));
@@ -1450,6 +1587,12 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
         if ((rc = gen_codes(ctx, total_steps, b->rows, b->cols, rng, &c16, d_depth ? 0u : (uint32_t)b->depth_u, n))) return rc;
         W.codes = ctx->buf[B_CODES].p;
         W.code_u16 = c16;
+    } else if (rng->mode == PCU_MODEL_WORDS) {
+        bool c16;
+        if ((rc = words_to_codes(ctx, wd, b->rows, b->cols, &c16))) return rc;
+        W.step_off = wd.step_off;
+        W.codes = ctx->buf[B_CODES].p;
+        W.code_u16 = c16;
     } else {
         W.model_seeds = d_mseed;
     }
@@ -1465,12 +1608,13 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
                              &lane_dmax, &geom.pos_min, &geom.pos_max)))
             return rc;
         if (geom.pos_min < gen_words) return fail(ctx, PCU_ERR_INVALID, "a state_pos is below 2*rows*cols*transitions");
-        lane = lane && lane_words <= MT_N - 1 && (rng->mode == PCU_MODEL_STREAM || 4 * lane_dmax <= MT_LAG - 3);
+        lane = lane && lane_words <= MT_N - 1 && (rng->mode != PCU_MODEL_PER_ROLLOUT || 4 * lane_dmax <= MT_LAG - 3);
         geom.words = (uint32_t)lane_words;
         geom.dmax = (uint32_t)lane_dmax;
     }
-    if (rng->mode == PCU_MODEL_STREAM) {
-        ctx->path = lane ? "lane_private_S" : "warp_private_S";
+    if (rng->mode != PCU_MODEL_PER_ROLLOUT) { /* modes S and W: the kernels take joint action codes */
+        const bool w = rng->mode == PCU_MODEL_WORDS;
+        ctx->path = lane ? (w ? "lane_private_W" : "lane_private_S") : (w ? "warp_private_W" : "warp_private_S");
         rc = lane ? launch_lane<KIND_TREE, 0>(ctx, W, geom) : launch_warp<KIND_TREE, 0>(ctx, W);
     } else {
         ctx->path = lane ? "lane_private_P" : "warp_private_P";
@@ -1516,7 +1660,34 @@ int rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+    WordsDev wd;
+    if (rng->mode == PCU_MODEL_WORDS && (rc = stage_words(ctx, b->mem, n, b->mem == PCU_MEM_HOST ? b->depth : nullptr,
+                                                          d_depth, b->depth_u, rng, wd)))
+        return rc;
     if ((rc = inputs_ready(ctx))) return rc;
+    if (rng->mode == PCU_MODEL_WORDS) { /* no state stream: one thread per rollout folds its words */
+        LeafParams L;
+        memset(&L, 0, sizeof(L));
+        L.n = n;
+        L.kind = KIND_MOLD;
+        L.cols = b->n_actions;
+        L.T = 1;
+        L.mrow = make_fold_const(b->n_actions);
+        L.mcol = make_fold_const(b->n_actions);
+        L.words = wd.words;
+        L.step_off = wd.step_off;
+        L.depth = d_depth;
+        L.depth_u = b->depth_u;
+        if ((rc = pack_source(ctx, od, n, &L.payoff))) return rc;
+        L.traj = od.traj;
+        L.traj_stride = out->traj_stride;
+        L.traj_hash = od.hash;
+        L.sums = od.sums;
+        ctx->path = "leaf_mold_W";
+        if ((rc = launch_leaf(ctx, L))) return rc;
+        if ((rc = pack_after(ctx, od, n, L.payoff))) return rc;
+        return finish_all(ctx, out, n, od, rng);
+    }
 
     if (!ctx->force_general && rng->mode == PCU_MODEL_STREAM && !b->depth && b->depth_u > 0 &&
         stream_fits(b->depth_u, (uint64_t)b->n_actions * b->n_actions)) {
@@ -1633,8 +1804,11 @@ void plan_shards(const Multi &M, uint64_t n, int mode, const uint16_t *depth, ui
     for (size_t g = 0; g < G; ++g) {
         plan[g].first = std::min<uint64_t>(n, g * per);
         plan[g].count = std::min<uint64_t>(n, plan[g].first + per) - plan[g].first;
-        if (mode == PCU_MODEL_STREAM) { /* ragged: prefix of the depths up to the shard (host memory) */
-            for (; next < plan[g].first; ++next) words += 4ull * depth[next];
+        if (mode != PCU_MODEL_PER_ROLLOUT) { /* model draws before the shard: prefix of the depths (host memory) */
+            if (depth)
+                for (; next < plan[g].first; ++next) words += 4ull * depth[next];
+            else
+                words = 4ull * depth_u * plan[g].first;
             plan[g].words_before = words;
         }
     }
@@ -1792,6 +1966,7 @@ int multi_rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, 
         sb.payoff_bias = off(b->payoff_bias, sp.first);
         pcu_model_rng sr = *rng;
         sr.seeds = off(rng->seeds, sp.first);
+        if (rng->mode == PCU_MODEL_WORDS) sr.words = rng->words + sp.words_before;
         if (rng->mode == PCU_MODEL_STREAM && !chunk) {
             const int e = shard_engine(rng, sp.words_before, engines[g]);
             if (e) return e;
@@ -1831,6 +2006,7 @@ int multi_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng
         sb.depth = off(b->depth, sp.first);
         pcu_model_rng sr = *rng;
         sr.seeds = off(rng->seeds, sp.first);
+        if (rng->mode == PCU_MODEL_WORDS) sr.words = rng->words + sp.words_before;
         if (rng->mode == PCU_MODEL_STREAM && !chunk) {
             const int e = shard_engine(rng, sp.words_before, engines[g]);
             if (e) return e;

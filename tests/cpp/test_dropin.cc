@@ -28,6 +28,7 @@
 #include <algorithm/tree-bandit/tree/tree-bandit.hh>
 #include <tree/tree.hh>
 
+#include <pinyon_cuda/batcher.hh>
 #include <pinyon_cuda/monte_carlo_model.hh>
 
 using RefTree = MonteCarloModel<RandomTree<>>;
@@ -35,6 +36,8 @@ using GpuTree = PinyonCuda::MonteCarloModel<RandomTree<>>;
 using RefMold = MonteCarloModel<MoldState<>>;
 using GpuMold = PinyonCuda::MonteCarloModel<MoldState<>>;
 using GpuTreePolicy = PinyonCuda::MonteCarloModel<RandomTree<>, true>;
+using BatchedTree = PinyonCuda::BatchedMonteCarloModel<RandomTree<>>;
+using BatchedMold = PinyonCuda::BatchedMonteCarloModel<MoldState<>>;
 
 // ---- the concepts every caller constrains its model with (src/model/model.hh:8-79)
 static_assert(IsValueModelTypes<GpuTree>);
@@ -50,6 +53,10 @@ static_assert(std::is_copy_constructible_v<GpuTree::Model>);
 static_assert(IsBanditAlgorithmTypes<Exp3<GpuTree>>);
 static_assert(IsSearchTypes<TreeBandit<Exp3<GpuTree>>>);
 static_assert(IsSearchTypes<TreeBandit<Exp3<GpuMold>>>);
+// ---- the batching adapter is a model like any other
+static_assert(IsValueModelTypes<BatchedTree> && IsSingleModelTypes<BatchedTree> && IsBatchModelTypes<BatchedTree>);
+static_assert(IsSearchTypes<TreeBandit<Exp3<BatchedTree>>> && IsSearchTypes<TreeBandit<Exp3<BatchedMold>>>);
+static_assert(std::is_copy_constructible_v<BatchedTree::Model>);
 
 static int g_failures = 0;
 #define CHECK(cond)                                                          \
@@ -341,6 +348,82 @@ static void test_threaded_copies() {
     std::printf("threaded copies ok\n");
 }
 
+// Root-parallel batching of UNMODIFIED TreeBandit (tree-bandit.hh:79-164): many independent searches in fibers, their
+// single-leaf inferences evaluated as batches in model-rng mode W.  Every tree must be identical to the same tree
+// searched alone over the reference model: same device seed, same model seed -> same root statistics, and the same
+// model engine afterwards.
+template <typename Types>
+static std::vector<double> root_stats(const typename Types::MatrixNode &root) {
+    std::vector<double> s{double(root.count_matrix_nodes()), double(root.stats.visits), double(root.stats.value_total.get_row_value())};
+    for (auto v : root.stats.row_visits) s.push_back(v);
+    for (auto v : root.stats.col_visits) s.push_back(v);
+    for (auto v : root.stats.row_gains) s.push_back(double(v));
+    return s;
+}
+
+static void test_batched_tree_bandit(size_t threads, size_t fibers, size_t iterations) {
+    using B = TreeBandit<Exp3<BatchedTree>>;
+    using R = TreeBandit<Exp3<RefTree>>;
+    const size_t trees = threads * fibers;
+    struct Cfg { uint64_t seed; size_t depth, rows, cols, T; };
+    const Cfg cfgs[] = {{0, 10, 3, 3, 1}, {5, 6, 3, 2, 2}};
+    for (const Cfg &c : cfgs) {
+        auto batcher = std::make_shared<PinyonCuda::LeafBatcher>(PinyonCuda::Device::shared(0), 512);
+        PinyonCuda::FiberPool pool(threads, fibers, {batcher});
+        std::vector<std::unique_ptr<B::MatrixNode>> roots(trees);
+        std::vector<uint64_t> engine_after(trees);
+        const RandomTree<>::State root_state{prng{c.seed}, c.depth, c.rows, c.cols, c.T};
+        pool.run(trees, [&](size_t k, size_t w) {
+            B::PRNG device{k};
+            B::Model model{prng{1000 + k}, pool.batcher(w)};
+            roots[k] = std::make_unique<B::MatrixNode>();
+            B::Search search{};
+            search.run_for_iterations(iterations, device, root_state, model, *roots[k]);
+            engine_after[k] = model.device.uniform_64();
+        });
+        size_t bad = 0;
+        for (size_t k = 0; k < trees; ++k) {
+            R::PRNG device{k};
+            R::Model model{prng{1000 + k}};
+            R::MatrixNode ref_root{};
+            R::Search search{};
+            search.run_for_iterations(iterations, device, root_state, model, ref_root);
+            bad += root_stats<R>(ref_root) != root_stats<B>(*roots[k]);
+            bad += model.device.uniform_64() != engine_after[k];
+        }
+        CHECK(bad == 0);
+        const auto st = batcher->stats();
+        CHECK(st.leaves > 0 && st.calls > 0 && st.leaves / st.calls > 1);
+        std::printf("batched TreeBandit<Exp3>: %zu trees x %zu iterations on %zu threads, %llu leaves in %llu GPU calls (%.0f per call), "
+                    "every tree == reference\n", trees, iterations, threads, (unsigned long long)st.leaves,
+                    (unsigned long long)st.calls, double(st.leaves) / double(st.calls));
+    }
+    {   // from a plain thread the same model is a synchronous drop-in (single leaves, flushed at once)
+        RefTree::Model ref{prng{4}};
+        BatchedTree::Model gpu{prng{4}};
+        const RandomTree<>::State root{prng{2}, 7, 4, 3, 2};
+        for (int i = 0; i < 30; ++i) {
+            RefTree::ModelOutput a;
+            BatchedTree::ModelOutput b;
+            ref.inference(RandomTree<>::State{root}, a);
+            gpu.inference(RandomTree<>::State{root}, b);
+            CHECK(same_value(a.value, b.value));
+        }
+        CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+        RefMold::Model mref{prng{6}};
+        BatchedMold::Model mgpu{prng{6}};
+        for (int i = 0; i < 10; ++i) {
+            RefMold::ModelOutput a;
+            BatchedMold::ModelOutput b;
+            mref.inference(MoldState<>::State{3, 9}, a);
+            mgpu.inference(MoldState<>::State{3, 9}, b);
+            CHECK(same_value(a.value, b.value));
+        }
+        CHECK(mref.device.uniform_64() == mgpu.device.uniform_64());
+    }
+    std::printf("batching adapter ok\n");
+}
+
 // ONE model.inference(batch_in, batch_out) on a context that spans several GPUs (pcu_create_multi: contiguous
 // rollout-index shards, per-shard slices of the one model stream, NCCL all-reduce of the counters) must equal the same
 // call on one GPU byte for byte, including model.device afterwards (monte-carlo-model.hh:58-67).  With one GPU in the box
@@ -402,6 +485,7 @@ int main(int argc, char **argv) {
             test_batch_inference();
             test_search_callers();
             test_threaded_copies();
+            test_batched_tree_bandit(4, 64, 200);
         } catch (const std::exception &e) {
             std::printf("FAIL exception: %s\n", e.what());
             ++g_failures;

@@ -142,6 +142,23 @@ def test_jump_family_slices_are_the_family(oracle):
         assert [e.next() for _ in range(100)] == exp.tolist(), (first, c)
 
 
+def test_take_raw_is_the_untempered_stream(oracle):
+    """pcu_mt_take_raw hands out the RAW words a mode-W rollout consumes and advances the engine like prng::discard."""
+    def temper(y):
+        y = y ^ (y >> np.uint32(11))
+        y = y ^ ((y << np.uint32(7)) & np.uint32(0x9D2C5680))
+        y = y ^ ((y << np.uint32(15)) & np.uint32(0xEFC60000))
+        return y ^ (y >> np.uint32(18))
+
+    for pre, n in ((0, 40), (600, 80), (623, 1), (624, 1300), (5, 0)):
+        e = Engine(17).discard(pre)
+        raw = e.take_raw(n)
+        exp = np.zeros(n + 3, np.uint32)
+        oracle.orc_mt_words(17, pre, n + 3, exp.ctypes.data)
+        assert np.array_equal(temper(raw), exp[:n])
+        assert [e.next() for _ in range(3)] == exp[n:].tolist()  # the engine continues behind the words taken
+
+
 def test_unpack2_roundtrip():
     rng = np.random.default_rng(0)
     for n in (0, 1, 3, 4, 5, 1001):

@@ -44,7 +44,8 @@ def test_dropin_host_logic_and_concepts():
 @pytest.mark.gpu
 def test_dropin_matches_reference_on_gpu():
     out = _run("--gpu")
-    for part in ("single inference ok", "batch inference ok", "TreeBandit<Exp3>", "OffPolicy<Exp3>", "threaded copies ok"):
+    for part in ("single inference ok", "batch inference ok", "TreeBandit<Exp3>", "OffPolicy<Exp3>", "threaded copies ok",
+                 "batching adapter ok", "every tree == reference"):
         assert part in out
 
 

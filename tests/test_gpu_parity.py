@@ -675,6 +675,80 @@ def test_state_table_is_cached_by_covering_range(ctx, oracle):
 
 
 # ---------------------------------------------------------------------------------------------
+# Mode W: every rollout brings the raw engine words of ITS OWN model (single-leaf inferences of many search trees
+# evaluated as one batch).  Reference semantics: Model{prng{s_i}}.inference(state_i), i.e. the oracle's mode P.
+
+
+def _words_for(mseeds, depth):
+    d = np.broadcast_to(np.asarray(depth, np.uint32), mseeds.shape)
+    return np.concatenate([Engine(int(s)).take_raw(4 * int(k)) for s, k in zip(mseeds, d)] or [np.zeros(0, np.uint32)])
+
+
+@pytest.mark.parametrize("shape", [(3, 3, 1, (0, 1)), (4, 3, 3, (3, 10)), (9, 9, 3, (0, 1)), (16, 17, 1, (0, 1))])
+@pytest.mark.parametrize("ragged", [False, True])
+def test_words_mode_leaves_of_one_root(ctx, oracle, shape, ragged):
+    """Leaves of searches from one root: one state stream, per-leaf positions, depths and biases -> k_leaf_table."""
+    rows, cols, T, thr = shape
+    rng = np.random.default_rng(rows + 10 * cols + 100 * T + ragged)
+    n = 4096 + 17
+    pre = rng.integers(0, 500, n).astype(np.uint32)
+    bias = rng.integers(-3, 4, n).astype(np.int32)
+    depth = rng.integers(1, 11, n).astype(np.uint32) if ragged else 7
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth, state_seed=21,
+                                      state_pre_discard=pre, transition_seed=4, payoff_bias=bias, model_seeds=mseeds)
+    words = _words_for(mseeds, depth)
+    dmax = int(np.max(depth))
+    out = dict(payoff=np.full(n, 255, np.uint8), traj=np.zeros((n, dmax, 3), np.uint8), traj_hash=np.zeros(n, np.uint32),
+               sums=np.zeros(8, np.uint64))
+    gen = 2 * rows * cols * T
+    ctx.rollout_random_tree(n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth.astype(np.uint16) if ragged else depth,
+                            state_seed=21, state_pos=pre + np.uint32(gen), transition_seed=4, payoff_bias=bias,
+                            model_words=words, traj_stride=dmax, **out)
+    assert ctx.last_path == "leaf_table_W"
+    check_same(out, exp, n)
+
+
+@pytest.mark.parametrize("T,path", [(1, "lane_private_W"), (2, "warp_private_W")])
+def test_words_mode_private_roots(ctx, oracle, T, path):
+    rng = np.random.default_rng(40 + T)
+    n = 1500
+    seeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    depth = rng.integers(1, 9, n).astype(np.uint32)
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    exp = loader.random_tree_rollouts(oracle, n, rows=3, cols=4, transitions=T, depth=depth, state_seed=seeds,
+                                      transition_seed=seeds, model_seeds=mseeds)
+    out = dict(payoff=np.full(n, 255, np.uint8), traj=np.zeros((n, 8, 3), np.uint8), traj_hash=np.zeros(n, np.uint32),
+               sums=np.zeros(8, np.uint64))
+    ctx.rollout_random_tree(n, rows=3, cols=4, transitions=T, depth=depth.astype(np.uint16), state_seed=seeds,
+                            transition_seed=seeds, model_words=_words_for(mseeds, depth), traj_stride=8, **out)
+    assert ctx.last_path == path
+    check_same(out, exp, n)
+
+
+def test_words_mode_mold_and_multi(ctx, mctx, oracle):
+    rng = np.random.default_rng(50)
+    n = 3000
+    depth = rng.integers(0, 12, n).astype(np.uint32)
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    words = _words_for(mseeds, depth)
+    exp = loader.mold_rollouts(oracle, n, n_actions=3, depth=depth, model_seeds=mseeds, want_traj=False)
+    for c in (ctx, mctx):
+        th = np.zeros(n, np.uint32)
+        sums = np.zeros(8, np.uint64)
+        c.rollout_mold(n, n_actions=3, depth=depth.astype(np.uint16), model_words=words, traj_hash=th, sums=sums)
+        assert c.last_path.startswith("leaf_mold_W")
+        assert np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
+    d1 = np.maximum(depth, 1)
+    words = _words_for(mseeds, d1)
+    exp = loader.random_tree_rollouts(oracle, n, rows=3, cols=3, depth=d1, state_seed=8, model_seeds=mseeds, want_traj=False)
+    got = dict(payoff=np.zeros(n, np.uint8), traj_hash=np.zeros(n, np.uint32), sums=np.zeros(8, np.uint64))
+    mctx.rollout_random_tree(n, rows=3, cols=3, depth=d1.astype(np.uint16), state_seed=8, model_words=words, **got)
+    assert mctx.last_path.startswith("leaf_table_W x")
+    check_same(got, exp, n)
+
+
+# ---------------------------------------------------------------------------------------------
 # One context over several GPUs (pcu_create_multi).  On a one-GPU box the shards share GPU 0 (listing a device twice is
 # allowed for exactly this): the shard plan, the per-shard slices of the global jump family, the output offsets and the
 # post-batch engine are the same code; only the reduction differs (a summing kernel instead of ncclAllReduce).
