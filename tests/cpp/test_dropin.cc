@@ -129,6 +129,51 @@ static void test_stream_locator() {
     std::printf("stream locator ok\n");
 }
 
+// The fiber scheduler of the batching adapter, without a GPU: fibers park on tickets, a pass resumes exactly those
+// whose ticket is ready, an exception inside a fiber surfaces in rethrow().
+static void test_fibers_host_only() {
+    PinyonCuda::FiberScheduler sched;
+    PinyonCuda::detail::tl_scheduler = &sched;
+    std::vector<PinyonCuda::Ticket> tickets(100);
+    long sum = 0;
+    for (int i = 0; i < 100; ++i)
+        sched.spawn(
+            [&, i] {
+                const double x = i * 1.5; /* a floating-point local must survive the switches */
+                for (int k = 0; k < 3; ++k) {
+                    PinyonCuda::FiberScheduler::current()->park(&tickets[i]);
+                    tickets[i].ready = 0;
+                    sum += long(x) + k;
+                }
+                if (i == 7) throw PinyonCuda::Error(PCU_ERR_INVALID, "fiber 7");
+            },
+            64 << 10);
+    CHECK(PinyonCuda::FiberScheduler::current() == nullptr); /* the main context is not a fiber */
+    auto r = sched.pass();
+    CHECK(r.first == 100 && r.second && sum == 0);
+    r = sched.pass();
+    CHECK(r.first == 100 && !r.second); /* every fiber is parked on an unready ticket */
+    for (int i = 0; i < 50; ++i) tickets[i].ready = 1;
+    r = sched.pass();
+    long expect = 0;
+    for (int i = 0; i < 50; ++i) expect += long(i * 1.5);
+    CHECK(r.second && sum == expect);
+    for (int round = 0; round < 8 && r.first; ++round) {
+        for (auto &t : tickets) t.ready = 1;
+        r = sched.pass();
+    }
+    CHECK(r.first == 0);
+    bool threw = false;
+    try {
+        sched.rethrow();
+    } catch (const PinyonCuda::Error &e) {
+        threw = std::string(e.what()) == "fiber 7";
+    }
+    CHECK(threw);
+    PinyonCuda::detail::tl_scheduler = nullptr;
+    std::printf("fibers ok\n");
+}
+
 static void test_loud_failure_without_gpu() {
     pcu_ctx *probe = nullptr;
     if (pcu_create(0, &probe) == PCU_OK) { /* a GPU is present: nothing to fail about */
@@ -477,6 +522,7 @@ int main(int argc, char **argv) {
     const bool gpu = argc > 1 && !std::strcmp(argv[1], "--gpu");
     test_engine_access();
     test_stream_locator();
+    test_fibers_host_only();
     if (!gpu) {
         test_loud_failure_without_gpu();
     } else {

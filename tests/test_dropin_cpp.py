@@ -34,7 +34,7 @@ def test_dropin_host_logic_and_concepts():
     """static_asserts of IsValue/Single/Batch/PolicyModelTypes and IsSearchTypes<TreeBandit<Exp3<Gpu>>> hold at
     compile time; engine access, the stream locator and the no-GPU failure are checked at run time."""
     out = _run("--cpu")
-    assert "engine access ok" in out and "stream locator ok" in out
+    assert "engine access ok" in out and "stream locator ok" in out and "fibers ok" in out
     import torch
 
     if not torch.cuda.is_available():
