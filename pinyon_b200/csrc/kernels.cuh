@@ -448,6 +448,12 @@ __device__ __forceinline__ uint32_t op_imadhi(uint32_t a, uint32_t b, uint32_t c
     return d;
 }
 
+__device__ __forceinline__ uint32_t op_imadwide_hi(uint32_t a, uint32_t b, uint32_t c) {
+    unsigned long long w;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(w) : "r"(a), "r"(b | 0x10000u), "l"((unsigned long long)c << 20));
+    return (uint32_t)(w >> 32);
+}
+
 /* Variants 0..2 feed the roofline; 3..6 are pipe probes used to design the generator:
  * 3: IMAD only; 4: IMAD.HI only; 5: LOP3, IMAD, LOP3 ... (2:1); 6: LOP3 + IMAD + IMAD.HI. */
 template <int VARIANT>
@@ -486,10 +492,22 @@ __global__ void __launch_bounds__(256) k_int_peak(uint32_t *out, uint32_t seed, 
                     a[j] = op_lop3(a[j], nb, k1);
                     a[j] = op_imad(a[j], k1, nb);
                     a[j] = ((j + u) & 1) ? op_lop3(a[j], k1, nb) : op_imad(a[j], nb, k1);
-                } else {
+                } else if (VARIANT == 6) {
                     a[j] = op_lop3(a[j], nb, k1);
                     a[j] = op_imadhi(a[j], k1, nb);
                     a[j] = ((j + u) & 1) ? op_lop3(a[j], k1, nb) : op_imad(a[j], nb, k1);
+                } else if (VARIANT == 7) { /* IMAD.WIDE only: a right shift as the high half of a 64-bit product */
+                    a[j] = op_imadwide_hi(a[j], k1, nb);
+                    a[j] = op_imadwide_hi(a[j], nb, k1);
+                    a[j] = op_imadwide_hi(nb, a[j], k1);
+                } else if (VARIANT == 8) { /* LOP3 : IMAD.WIDE 2 : 1 */
+                    a[j] = op_lop3(a[j], nb, k1);
+                    a[j] = op_imadwide_hi(a[j], k1, nb);
+                    a[j] = op_lop3(a[j], k1, nb);
+                } else { /* 9: SHF only */
+                    a[j] = op_shf(a[j], nb);
+                    a[j] = op_shf(a[j], k1);
+                    a[j] = op_shf(nb, a[j]);
                 }
             }
         }

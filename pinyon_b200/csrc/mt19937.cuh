@@ -68,15 +68,21 @@ __device__ __forceinline__ uint32_t mod64(uint32_t hi, uint32_t lo, const ModCon
 __device__ __forceinline__ uint32_t mt_twist_dev(uint32_t a, uint32_t b, uint32_t c) {
     uint32_t y, x;
     asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(y) : "r"(a), "r"(b), "r"(0x80000000u)); /* (a & m) | (b & ~m) */
-    uint32_t mag; /* written as a multiply-add so that it issues on the FMA pipe */
-    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(mag) : "r"(b & 1u), "r"(0x9908b0dfu), "r"(0u));
-    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(x) : "r"(c), "r"(y >> 1), "r"(mag));
+    const uint32_t s = y >> 1;
+    /* (y & 1) * matrix without touching the ALU pipe: y & 1 = y - 2 (y >> 1), so the product is
+     * y * matrix - (y >> 1) * (2 * matrix) in wrapping arithmetic: two multiply-adds on the FMA pipe
+     * (the twist is then 3 ALU + 2 FMA instructions; the ALU pipe is the one the generator saturates) */
+    uint32_t t, mag;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(t) : "r"(s), "r"(0u - 2u * 0x9908b0dfu), "r"(0u));
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(mag) : "r"(y), "r"(0x9908b0dfu), "r"(t));
+    asm("lop3.b32 %0, %1, %2, %3, 0x96;" : "=r"(x) : "r"(c), "r"(s), "r"(mag));
     return x;
 }
 
 /* Per-modulus constants of the folded 64-bit reduction below (n <= 256). */
 struct FoldConst {
     uint32_t n, m, c32, k1, k2; /* m = floor(2^32 / n); see mod64_fold */
+    uint32_t negn;              /* -n: the remainder is one multiply-add, q * (-n) + s */
 };
 
 inline FoldConst make_fold_const(uint32_t n) {
@@ -88,6 +94,7 @@ inline FoldConst make_fold_const(uint32_t n) {
     f.c32 = (n <= 1) ? 0u : (uint32_t)(0x100000000ull % n);
     f.k1 = c48 - 65536u * f.c32; /* mod 2^32 */
     f.k2 = c16 - 65536u;
+    f.negn = 0u - n;
     return f;
 }
 
@@ -101,7 +108,10 @@ inline FoldConst make_fold_const(uint32_t n) {
  * word-by-word reduction (mod64) were the most expensive part of a model step. */
 __device__ __forceinline__ uint32_t mod64_fold(uint32_t hi, uint32_t lo, const FoldConst &f) {
     const uint32_t s = (hi >> 16) * f.k1 + hi * f.c32 + (lo >> 16) * f.k2 + lo;
-    return mod32(s, f.n, f.m);
+    const uint32_t q = __umulhi(s, f.m); /* floor(s / n) or one less */
+    uint32_t r;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(q), "r"(f.negn), "r"(s));
+    return min(r, r + f.negn);
 }
 
 /* prng::uniform() (random.hh:23): generate_canonical<double,53> over a 32-bit engine;

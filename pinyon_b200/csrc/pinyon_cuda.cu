@@ -602,9 +602,9 @@ template <int KIND, typename CodeT>
 int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t smem) {
     auto kern = tab_smem ? k_stream2<KIND, CodeT, true> : k_stream2<KIND, CodeT, false>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned ctas = (P.streams + GW_PAIRS - 1) / GW_PAIRS;
+    const unsigned ctas = (P.streams + SP_STREAMS - 1) / SP_STREAMS;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    kern<<<ctas, GW_PAIRS * 64, smem, ctx->stream>>>(P);
+    kern<<<ctas, SP_THREADS, smem, ctx->stream>>>(P);
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->ev_valid = true;
     ctx->launches++;
@@ -614,12 +614,19 @@ int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t sm
 
 constexpr size_t SMEM_LIMIT = 200 * 1024;
 
-/* Whether the fused kernel's per-generator code queue (two buffers of 32 rollouts x depth codes) fits in shared
- * memory; deeper batches take the general path (codes through HBM). */
-bool stream_fits(uint32_t depth, uint64_t actions) {
-    uint64_t qlen = 1024;
-    while (qlen < 2ull * 64 * depth + 2 * GW_PASS_STEPS) qlen <<= 1;
-    const size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + (size_t)GW_PAIRS * (qlen + 16) * (actions <= 256 ? 1 : 2) + 16;
+/* Code queue of one stream: a whole number of batches (so a batch never wraps), holding a batch plus the pass being
+ * consumed and the pass being generated. */
+uint32_t stream_ring_codes(uint32_t rb, uint32_t depth) {
+    const uint64_t b = (uint64_t)rb * depth;
+    const uint64_t slots = 2 + (2 * GW_PASS_STEPS + b - 1) / b;
+    return (uint32_t)std::min<uint64_t>(slots * b, 0xffffffffull);
+}
+
+/* Whether the fused kernel's per-stream code queue fits in shared memory; deeper batches take the general path
+ * (codes through HBM). */
+bool stream_fits(uint32_t depth, uint64_t actions, uint32_t rb = 32) {
+    const uint64_t ring = (uint64_t)stream_ring_codes(rb, depth);
+    const size_t smem = (size_t)SP_STREAMS * GW_RING * 4 + (size_t)SP_STREAMS * (ring + 16) * (actions <= 256 ? 1 : 2) + 16;
     return smem <= SMEM_LIMIT;
 }
 
@@ -646,8 +653,11 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     ctx->last_chunk = P.chunk;
     ctx->last_streams = P.streams;
     P.rb = od.packed ? 128 : ctx->rb; /* the packed output is one byte per lane: four consecutive rollouts */
-    P.qlen = 1024;
-    while (P.qlen < 2ull * P.rb * P.depth + 2 * GW_PASS_STEPS) P.qlen <<= 1;
+    if (!stream_fits(P.depth, (uint64_t)rows * P.cols, P.rb)) P.rb = 32;
+    P.bcodes = P.rb * P.depth;
+    P.ring_codes = stream_ring_codes(P.rb, P.depth);
+    if (P.chunk * (uint64_t)P.depth >= (1ull << 32))
+        return fail(ctx, PCU_ERR_UNSUPPORTED, "a model stream of %llu x %u steps exceeds 2^32", (unsigned long long)P.chunk, P.depth);
     int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, first_stream, P.streams, 4ull * P.depth * P.chunk);
     if (rc) return rc;
     P.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
@@ -661,8 +671,8 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.vec_ok = (P.chunk % 4 == 0) && ((uintptr_t)od.payoff % 4 == 0) && ((uintptr_t)od.hash % 16 == 0);
     (void)out;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
-    const size_t queue_bytes = (size_t)GW_PAIRS * (P.qlen + 16) * (code8 ? 1 : 2);
-    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + queue_bytes + 16;
+    const size_t queue_bytes = (size_t)SP_STREAMS * (P.ring_codes + 16) * (code8 ? 1 : 2);
+    size_t smem = (size_t)SP_STREAMS * GW_RING * 4 + queue_bytes + 16;
     const size_t tab_bytes = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
     bool tab_smem = false;
     if (KIND == KIND_TREE && smem + tab_bytes + 16 <= SMEM_LIMIT) {
@@ -2165,7 +2175,10 @@ int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_se
             case 3: k_int_peak<3><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
             case 4: k_int_peak<4><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
             case 5: k_int_peak<5><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
-            default: k_int_peak<6><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 6: k_int_peak<6><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 7: k_int_peak<7><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            case 8: k_int_peak<8><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
+            default: k_int_peak<9><<<blocks, threads, 0, ctx->stream>>>(d, 12345u + r, iters); break;
         }
         ctx->launches++;
         CU(cudaEventRecord(e1, ctx->stream));

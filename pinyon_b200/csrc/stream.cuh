@@ -11,12 +11,12 @@
 //     word first, random.hh:26,28) live in one thread: no shuffles, no redundant lanes;
 //   - no CTA barrier anywhere: a group ends with __syncwarp().
 //
-// Fused kernel (k_stream2): CTA = GW_PAIRS generator warps + GW_PAIRS consumer warps.
-// Generator g streams joint action codes (row * cols + col) into a double-buffered
-// shared-memory queue; consumer g (same SM sub-partition: warp id + GW_PAIRS) plays
-// RB rollouts per buffer, one or two per lane, against the shared state-stream table.
-// Hand-off is by named barriers (bar.sync / bar.arrive, 64 threads), so the consumer's
-// latency-bound table walks overlap the generator's ALU work on the same scheduler.
+// Fused kernel (k_stream2): CTA = SP_STREAMS streams x 3 warps.  Two generator warps share a
+// stream and alternate its 224-word groups (the recurrence of one group runs beside the
+// tempering of the previous one); they put joint action codes (row * cols + col) into a
+// shared-memory queue, and the stream's consumer warp plays the rollouts whose codes are
+// complete, one to four per lane, against the shared state-stream table.  Hand-off is by named
+// barriers (bar.sync): a waiting warp takes no issue slots.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -32,7 +32,6 @@ constexpr int GW_STEPS = 2 * GW_ACTIVE;   /* model steps per group */
 constexpr int GW_WORDS = 4 * GW_STEPS;    /* 224 <= 227 */
 constexpr int GW_RING = 4 * GW_WORDS;     /* 896 >= 624 + 224: four group slots */
 constexpr int GW_PASS_STEPS = 4 * GW_STEPS; /* model steps per pass (one turn of the ring) */
-constexpr int GW_PAIRS = 4;               /* generator/consumer warp pairs per CTA */
 
 /* Ring slot of (compile-time offset C) + 4 * lane; the wrap test is only emitted for the
  * few offsets whose 28 lanes straddle the end of the ring. */
@@ -103,15 +102,7 @@ __device__ __forceinline__ void gw_dump_window(const uint32_t *ring, uint32_t w_
     for (int i = lane; i < MT_N; i += 32) dst[i] = ring[(w_end + 48 + i) % GW_RING];
 }
 
-/* Named barriers between a generator warp and its consumer warp (64 threads each): a waiting
- * warp takes no issue slots, unlike a polling loop on the same scheduler. */
-__device__ __forceinline__ void nb_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
-__device__ __forceinline__ void nb_arrive(int id) {
-    __threadfence_block();
-    asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
-}
-
-/* The generator loop, software pipelined: while the 8 words of group g are tempered and reduced
+/* The single-warp generator loop (k_gen_codes2), software pipelined: while the 8 words of group g are tempered and reduced
  * to action codes (ALU work with no memory dependence), the operands of group g + 1 are already
  * in flight from the ring; its twist and store close the iteration.  A pass is four groups
  * (896 words: one turn of the ring).  `sink` receives the codes:
@@ -173,8 +164,9 @@ struct Stream2Params {
     uint64_t chunk;   /* rollouts per stream */
     uint32_t streams; /* ceil(n / chunk) */
     uint32_t depth;   /* uniform depth_bound / max_depth */
-    uint32_t rb;      /* rollouts per consumer batch */
-    uint32_t qlen;    /* codes per queue ring: power of two >= 2 * rb * depth + 448 */
+    uint32_t rb;      /* rollouts per consumer batch: 32, 64 or 128 */
+    uint32_t bcodes;  /* rb * depth: codes of one batch */
+    uint32_t ring_codes; /* code queue length: a whole number of batches, >= bcodes + 2 passes */
     uint32_t cols, T, gen_words;
     FoldConst mrow, mcol;
     const uint32_t *checkpoints; /* [streams][624] raw words preceding each stream's first model word */
@@ -195,43 +187,90 @@ struct Stream2Params {
     uint32_t *end_window; /* [624] raw words preceding the first model word after the batch */
 };
 
-struct RolloutAcc {
-    unsigned long long w = 0, d = 0, l = 0, h = 0, n = 0;
-};
+/* One model stream = THREE warps on one SM sub-partition (warp ids s, 4 + s, 8 + s of the CTA):
+ *   generator halves A and B   share the stream's 896-word ring and alternate its 224-word groups: A makes groups
+ *        0, 2, 4, ..., B groups 1, 3, 5, ...  A group is (1) the recurrence — operands from the ring, twist, store —
+ *        and (2) temper + uniform_int reduction of its eight words per lane to two joint action codes, pure register
+ *        arithmetic.  Group g + 1 needs group g's words (X[n-227]), so part (1) is a serial chain through the ring;
+ *        part (2) is three quarters of the instructions and depends on nothing.  After storing its group a half meets
+ *        its partner at a named barrier (64 threads) and then does part (2) WHILE the partner runs part (1) of the next
+ *        group: the scheduler always has an independent instruction stream beside the serial one, which one
+ *        generator warp per stream did not give it (r1 ncu: one warp issued every 2.4 cycles, ALU pipe 62 % busy),
+ *        and a second STREAM per scheduler would cost a second jump-ahead checkpoint.
+ *   consumer                    plays the rollouts whose codes are complete, once per pass.
+ * Hand-off generator -> consumer: ONE named barrier per stream and pass (96 threads).  The consumer plays the
+ * batches completed by pass j while the halves generate pass j + 1; the code queue holds a batch plus two passes. */
+constexpr int SP_STREAMS = 4;               /* streams per CTA */
+constexpr int SP_THREADS = SP_STREAMS * 96; /* 12 warps */
 
-/* Code queue between a generator warp and its consumer: a ring of Q (power of two) codes
- * indexed by absolute step number.  Hand-off is per pass (224 codes) over four named barriers,
- * full[2] = bar + {0,1} and empty[2] = bar + {2,3}, indexed by pass parity: the generator
- * arrives on full[j & 1] after pass j and, from pass 2 on, first waits on empty[j & 1], which the
- * consumer arrives on once it has played every rollout completed by pass j - 2.  Unplayed codes
- * are then less than one batch plus two passes: Q >= 2 * rb * depth + 448 holds them. */
+__device__ __forceinline__ void bar_sync(int id, int threads) {
+    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+/* Joint action codes of one group into the stream's code queue: a ring of `ring_codes` codes indexed by the absolute
+ * step number modulo its length.  Lane l holds steps 56 g + l and 56 g + 28 + l. */
 template <typename CodeT>
-struct QueueSink {
-    CodeT *queue; /* Q codes, then a dummy slot for the shadow lanes */
-    uint32_t qmask;
-    int bar;
-    int lane;
-    uint32_t qpos = 0; /* (56 * g) & qmask for the next group */
-
-    __device__ __forceinline__ void begin_pass(uint64_t pass) {
-        if (pass >= 2) nb_sync(bar + 2 + (int)(pass & 1));
-    }
-    __device__ __forceinline__ void put(uint64_t, uint32_t c0, uint32_t c1, bool active) {
-        const uint32_t i0 = active ? ((qpos + lane) & qmask) : qmask + 1;
-        const uint32_t i1 = active ? ((qpos + GW_ACTIVE + lane) & qmask) : qmask + 1;
-        queue[i0] = (CodeT)c0;
-        queue[i1] = (CodeT)c1;
-        qpos = (qpos + GW_STEPS) & qmask;
-    }
-    __device__ __forceinline__ void end_pass(uint64_t pass) {
-        __syncwarp();
-        nb_arrive(bar + (int)(pass & 1));
+struct PairQueue {
+    CodeT *queue;
+    uint32_t ring_codes;
+    uint32_t qpos; /* (56 g) mod ring_codes for this half's next group */
+    __device__ __forceinline__ void put(uint32_t c0, uint32_t c1, int lane, bool active) {
+        uint32_t i0 = qpos + lane, i1 = qpos + GW_ACTIVE + lane;
+        i0 = min(i0, i0 - ring_codes); /* unsigned: wraps when i0 >= ring_codes */
+        i1 = min(i1, i1 - ring_codes);
+        if (active) {
+            queue[i0] = (CodeT)c0;
+            queue[i1] = (CodeT)c1;
+        }
+        qpos += 2 * GW_STEPS; /* this half's next group is two groups on */
+        qpos = min(qpos, qpos - ring_codes);
     }
 };
 
-/* Consumer side: one rollout = `d` codes of the queue walked over the shared state stream.
- * Codes of a rollout are contiguous in the ring (index & qmask).  All return the trajectory
- * hash; TRAJ also writes (row, col, chance) bytes. */
+template <int HALF, int PH, typename CodeT>
+__device__ __forceinline__ void pair_phase(uint32_t *ring, int l4, int lane, bool active, const FoldConst &mrow,
+                                           const FoldConst &mcol, uint32_t cols, PairQueue<CodeT> &q, int pair_bar) {
+    constexpr bool MINE = (PH & 1) == HALF;
+    uint4 x0 = make_uint4(0, 0, 0, 0), x1 = x0;
+    if (MINE) { /* part (1): the recurrence for this group */
+        GwOps o;
+        gw_load<PH>(ring, l4, o);
+        x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);
+        x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);
+        gw_store<PH>(ring, l4, active, x0, x1);
+    }
+    bar_sync(pair_bar, 64); /* the group is in the ring: the partner may start the next one */
+    if (MINE) {             /* part (2), beside the partner's part (1) */
+        const uint32_t c0 = gw_code(x0, mrow, mcol, cols);
+        const uint32_t c1 = gw_code(x1, mrow, mcol, cols);
+        q.put(c0, c1, lane, active);
+    }
+}
+
+template <int HALF, typename CodeT>
+__device__ __forceinline__ void pair_generate(uint32_t *ring, CodeT *queue, uint32_t ring_codes, uint32_t groups, int lane,
+                                              const FoldConst &mrow, const FoldConst &mcol, uint32_t cols, int pair_bar,
+                                              int pass_bar) {
+    const bool active = lane < GW_ACTIVE;
+    const int l4 = 4 * (active ? lane : GW_ACTIVE - 1); /* lanes 28..31 shadow lane 27, stores predicated off */
+    PairQueue<CodeT> q{queue, ring_codes, (uint32_t)(GW_STEPS * HALF)};
+    for (uint32_t g = 0; g < groups; g += 4) {
+        const uint32_t rest = groups - g; /* >= 1; the same in both halves */
+        pair_phase<HALF, 0>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
+        if (rest > 1) pair_phase<HALF, 1>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
+        if (rest > 2) pair_phase<HALF, 2>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
+        if (rest > 3) pair_phase<HALF, 3>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
+        bar_sync(pass_bar, 96); /* the pass is in the queue (both halves) and the consumer is done with the pass
+                                   before the previous one */
+    }
+}
+
+/* Per-lane counters of a consumer warp: payoffs are 0, 1, 2, so the three outcome counts come from two sums. */
+struct RolloutAcc {
+    uint32_t pay_sum = 0, draws = 0, n = 0;
+    unsigned long long h = 0;
+};
+
 template <bool TRAJ>
 __device__ __forceinline__ void put_traj(uint8_t *tr, uint32_t s, uint32_t code, uint32_t cols, uint32_t ch,
                                          uint32_t stride) {
@@ -243,77 +282,55 @@ __device__ __forceinline__ void put_traj(uint8_t *tr, uint32_t s, uint32_t code,
     }
 }
 
-template <bool TRAJ, typename CodeT>
-__device__ __forceinline__ uint32_t walk_mold(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
-                                              uint8_t *tr, uint32_t tstride) {
-    uint32_t h = PCU_HASH_INIT;
-#pragma unroll 5
-    for (uint32_t s = 0; s < d; ++s) {
-        const uint32_t code = queue[(qb + s) & qmask];
-        h = hash_step(h, code, 0);
-        put_traj<TRAJ>(tr, s, code, cols, 0, tstride);
+/* One batch of rb = 32 Q rollouts whose codes are complete; `q` points at the batch's first code (a batch never wraps
+ * in the queue: its length is a whole number of batches).  Lane l plays the Q CONSECUTIVE rollouts Q l .. Q l + Q - 1,
+ * their table walks interleaved (Q independent chains of dependent shared-memory loads), and stores their outputs as
+ * ONE vector: Q payoff bytes (Q = 4: a warp writes one contiguous 128-byte line, which is also one PCIe write when the
+ * payoffs go straight to pinned host memory), or one byte of 2-bit payoffs (Q = 4, pcu_out.payoff_packed2), and Q
+ * trajectory hashes.  Lanes past the end of a partial batch replay their last live rollout and store nothing for it.
+ * A step of the walk: T == 1: chance strategies are all 1, chance action 0 (random-tree.hh:115-135 with p - 1 <= 0):
+ * discard(row cols + col) (:88-89), one bias draw (:97), then 2 rows cols strategy draws; T > 1: the chance action
+ * of the chosen cell comes from the per-position table. */
+/* The state-stream table: in shared memory (32-bit shared addresses, LDS) when it fits, else read-only global
+ * memory.  A generic pointer would cost a 64-bit add and a generic load per table access. */
+template <bool SMEM>
+struct TabAccess;
+template <>
+struct TabAccess<true> {
+    using Addr = uint32_t;
+    static __device__ __forceinline__ Addr at(const uint8_t *tab, uint32_t idx) {
+        return (uint32_t)__cvta_generic_to_shared(tab) + idx;
     }
-    return h;
-}
-
-/* T == 1: chance strategies are all 1, chance action 0 (random-tree.hh:115-135 with p - 1 <= 0);
- * a step is discard(row * cols + col), one bias draw, then 2 * rows * cols strategy draws. */
-template <bool TRAJ, typename CodeT>
-__device__ __forceinline__ uint32_t walk_tree1(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
-                                               const int8_t *tb, uint32_t p, uint32_t adv, int &bias, uint8_t *tr,
-                                               uint32_t tstride) {
-    uint32_t h = PCU_HASH_INIT;
-    int b = bias;
-#pragma unroll 5
-    for (uint32_t s = 0; s < d; ++s) {
-        const uint32_t code = queue[(qb + s) & qmask];
-        const uint32_t t = p + code; /* discard(row*cols + col): random-tree.hh:88-89 */
-        b += tb[t];
-        p = t + adv;
-        h = hash_step(h, code, 0);
-        put_traj<TRAJ>(tr, s, code, cols, 0, tstride);
+    static __device__ __forceinline__ int s8(Addr a) {
+        int v;
+        asm("ld.shared.s8 %0, [%1];" : "=r"(v) : "r"(a));
+        return v;
     }
-    bias = b;
-    return h;
-}
-
-/* T > 1: the chance action of the chosen cell comes from the per-position table. */
-template <bool TRAJ, typename CodeT>
-__device__ __forceinline__ uint32_t walk_treeT(const CodeT *queue, uint32_t qmask, uint32_t qb, uint32_t d, uint32_t cols,
-                                               uint32_t T, const int8_t *tb, const uint8_t *tch, uint32_t p,
-                                               uint32_t gen_words, int &bias, uint8_t *tr, uint32_t tstride) {
-    uint32_t h = PCU_HASH_INIT;
-    int b = bias;
-    uint32_t gb = p - gen_words; /* where the current chance strategies were drawn */
-#pragma unroll 5
-    for (uint32_t s = 0; s < d; ++s) {
-        const uint32_t code = queue[(qb + s) & qmask];
-        const uint32_t st = code * T;
-        const uint32_t ch = tch[gb + 2 * st];
-        const uint32_t t = gb + gen_words + st + ch; /* discard(get_transition_idx): random-tree.hh:88-89,149-152 */
-        b += tb[t];
-        gb = t + 2;
-        h = hash_step(h, code, ch);
-        put_traj<TRAJ>(tr, s, code, cols, ch, tstride);
+    static __device__ __forceinline__ uint32_t u8(Addr a) {
+        uint32_t v;
+        asm("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+        return v;
     }
-    bias = b;
-    return h;
-}
+};
+template <>
+struct TabAccess<false> {
+    using Addr = const uint8_t *;
+    static __device__ __forceinline__ Addr at(const uint8_t *tab, uint32_t idx) { return tab + idx; }
+    static __device__ __forceinline__ int s8(Addr a) { return (int)(int8_t)__ldg(a); }
+    static __device__ __forceinline__ uint32_t u8(Addr a) { return __ldg(a); }
+};
 
-/* One batch of rb = 32 Q rollouts whose codes are complete.  Lane l plays the Q CONSECUTIVE rollouts
- * Q l .. Q l + Q - 1 of the batch, their table walks interleaved (Q independent chains of dependent
- * shared-memory loads), and stores their outputs as ONE vector: Q payoff bytes (Q = 4: a warp writes one
- * contiguous 128-byte line, which is also one PCIe write when the payoffs go straight to pinned host memory),
- * or one byte of 2-bit payoffs (Q = 4, pcu_out.payoff_packed2), and Q trajectory hashes.  Lanes past the end of
- * a partial batch replay their last live rollout and store nothing for it. */
-template <int KIND, typename CodeT, int Q>
-__device__ __forceinline__ void consume_batch(const Stream2Params &P, const CodeT *queue, uint32_t qmask, const uint8_t *tab,
-                                              uint64_t i0, uint32_t kbase, uint32_t live, int lane, RolloutAcc &acc) {
+template <int KIND, typename CodeT, int Q, bool TAB_SMEM>
+__device__ __forceinline__ void consume_batch(const Stream2Params &P, const CodeT *q, const uint8_t *tab, uint64_t i0,
+                                              uint32_t live, int lane, RolloutAcc &acc) {
+    using TA = TabAccess<TAB_SMEM>;
     const uint32_t d = P.depth, T = P.T;
     const uint32_t rl = (uint32_t)Q * lane;
     if (rl >= live) return;
     const uint32_t mine = (live - rl < (uint32_t)Q) ? live - rl : (uint32_t)Q; /* 1..Q rollouts of this lane */
     const uint64_t il = i0 + rl;
+    const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
+    const uint8_t *tch = tab + P.tab_len;
     uint32_t h[Q], pay[Q];
     if (P.traj) { /* trajectories: one rollout at a time (tests and small batches) */
 #pragma unroll
@@ -322,34 +339,43 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
             pay[j] = 0;
             if ((uint32_t)j >= mine) continue;
             const uint64_t i = il + j;
-            const uint32_t qb = kbase + (rl + j) * d;
+            const CodeT *qc = q + (rl + j) * d;
             uint8_t *tr = P.traj + (size_t)i * P.traj_stride * 3;
             if (KIND == KIND_MOLD) {
-                h[j] = walk_mold<true>(queue, qmask, qb, d, P.cols, tr, P.traj_stride);
+                for (uint32_t s = 0; s < d; ++s) {
+                    const uint32_t code = qc[s];
+                    h[j] = hash_step(h[j], code, 0);
+                    put_traj<true>(tr, s, code, P.cols, 0, P.traj_stride);
+                }
             } else {
-                const uint32_t p = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base;
+                uint32_t g = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base - P.gen_words;
                 int bias = P.bias ? P.bias[i] : P.bias_u;
-                const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
-                if (T == 1)
-                    h[j] = walk_tree1<true>(queue, qmask, qb, d, P.cols, tb, p, 2 + P.gen_words, bias, tr, P.traj_stride);
-                else
-                    h[j] = walk_treeT<true>(queue, qmask, qb, d, P.cols, T, tb, tab + P.tab_len, p, P.gen_words, bias, tr,
-                                            P.traj_stride);
+                for (uint32_t s = 0; s < d; ++s) {
+                    const uint32_t code = qc[s];
+                    const uint32_t st = code * T;
+                    const uint32_t ch = T > 1 ? (uint32_t)tch[g + 2 * st] : 0u;
+                    const uint32_t t = g + P.gen_words + st + ch; /* discard(get_transition_idx): :88-89,149-152 */
+                    bias += tb[t];
+                    g = t + 2;
+                    h[j] = hash_step(h[j], code, ch);
+                    put_traj<true>(tr, s, code, P.cols, ch, P.traj_stride);
+                }
                 pay[j] = (uint32_t)((bias > 0) - (bias < 0) + 1);
             }
             for (uint32_t s = d; s < P.traj_stride; ++s) tr[3 * s] = tr[3 * s + 1] = tr[3 * s + 2] = 0;
         }
     } else {
-        uint32_t qb[Q], p[Q];
+        const CodeT *qc[Q];
+        typename TA::Addr p[Q]; /* table address of the next discard: one add per step instead of base + index */
         int bias[Q];
 #pragma unroll
         for (int j = 0; j < Q; ++j) {
             const uint32_t jj = ((uint32_t)j < mine) ? (uint32_t)j : mine - 1;
             h[j] = PCU_HASH_INIT;
             pay[j] = 0;
-            qb[j] = kbase + (rl + jj) * d;
+            qc[j] = q + (rl + jj) * d;
             if (KIND == KIND_TREE) {
-                p[j] = (P.state_pos ? P.state_pos[il + jj] : P.state_pos_u) - P.tab_base;
+                p[j] = TA::at(tab, (P.state_pos ? P.state_pos[il + jj] : P.state_pos_u) - P.tab_base);
                 bias[j] = P.bias ? P.bias[il + jj] : P.bias_u;
             }
         }
@@ -357,39 +383,34 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
 #pragma unroll 2
             for (uint32_t s = 0; s < d; ++s) {
 #pragma unroll
-                for (int j = 0; j < Q; ++j) h[j] = hash_step(h[j], queue[(qb[j] + s) & qmask], 0);
+                for (int j = 0; j < Q; ++j) h[j] = hash_step(h[j], qc[j][s], 0);
             }
         } else if (T == 1) {
-            /* chance strategies are all 1, chance action 0 (random-tree.hh:115-135 with p - 1 <= 0): a step is
-             * discard(row * cols + col), one bias draw, then 2 * rows * cols strategy draws */
-            const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
             const uint32_t adv = 2 + P.gen_words;
 #pragma unroll 2
             for (uint32_t s = 0; s < d; ++s) {
 #pragma unroll
                 for (int j = 0; j < Q; ++j) {
-                    const uint32_t code = queue[(qb[j] + s) & qmask];
-                    const uint32_t t = p[j] + code; /* discard(row*cols + col): random-tree.hh:88-89 */
-                    bias[j] += tb[t];
+                    const uint32_t code = qc[j][s];
+                    const typename TA::Addr t = p[j] + code;
+                    bias[j] += TA::s8(t);
                     p[j] = t + adv;
                     h[j] = hash_step(h[j], code, 0);
                 }
             }
         } else {
-            const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
-            const uint8_t *tch = tab + P.tab_len;
-            const uint32_t gen = P.gen_words;
+            const uint32_t gen = P.gen_words, tl = P.tab_len;
 #pragma unroll
             for (int j = 0; j < Q; ++j) p[j] -= gen; /* where the current chance strategies were drawn */
 #pragma unroll 2
             for (uint32_t s = 0; s < d; ++s) {
 #pragma unroll
                 for (int j = 0; j < Q; ++j) {
-                    const uint32_t code = queue[(qb[j] + s) & qmask];
+                    const uint32_t code = qc[j][s];
                     const uint32_t st = code * T;
-                    const uint32_t ch = tch[p[j] + 2 * st];
-                    const uint32_t t = p[j] + gen + st + ch; /* discard(get_transition_idx): random-tree.hh:88-89,149-152 */
-                    bias[j] += tb[t];
+                    const uint32_t ch = TA::u8(p[j] + (tl + 2 * st)); /* the chance table follows the bias table */
+                    const typename TA::Addr t = p[j] + (gen + st + ch);
+                    bias[j] += TA::s8(t);
                     p[j] = t + 2;
                     h[j] = hash_step(h[j], code, ch);
                 }
@@ -407,17 +428,12 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
         if ((uint32_t)j < mine) {
             bytes |= pay[j] << (8 * j);
             packed |= pay[j] << (2 * j);
-            if (KIND == KIND_MOLD) {
-                acc.d += 1;
-            } else {
-                acc.w += (pay[j] == 2);
-                acc.d += (pay[j] == 1);
-                acc.l += (pay[j] == 0);
-            }
+            acc.pay_sum += pay[j];
+            acc.draws += pay[j] & 1u;
             acc.h += h[j];
-            acc.n += 1;
         }
     }
+    acc.n += mine;
     if (P.payoff) {
         if (Q == 4 && P.vec_ok && mine == 4) {
             *reinterpret_cast<uint32_t *>(P.payoff + il) = bytes;
@@ -441,100 +457,103 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
     }
 }
 
-/* The consumer warp of one stream: waits for each pass of its generator and plays every batch the pass completed. */
-template <int KIND, typename CodeT, int Q>
-__device__ __forceinline__ void consume_stream(const Stream2Params &P, const CodeT *queue, uint32_t qmask, const uint8_t *tab,
-                                               int bar, uint64_t first, uint64_t cnt, int lane, RolloutAcc &acc) {
+/* The consumer warp of one stream: meets the generator halves at the pass barrier and plays every batch the pass
+ * completed.  All stream-local arithmetic is 32-bit (a stream is < 2^32 steps: host-checked). */
+template <int KIND, typename CodeT, int Q, bool TAB_SMEM>
+__device__ __forceinline__ void consume_stream(const Stream2Params &P, const CodeT *queue, const uint8_t *tab, int pass_bar,
+                                               uint64_t first, uint32_t cnt, int lane, RolloutAcc &acc) {
     constexpr uint32_t RB = 32u * Q;
     const uint32_t d = P.depth;
-    const uint64_t total_steps = cnt * d;
-    const uint64_t nbuf = (cnt + RB - 1) / RB;
-    const uint64_t npass = (total_steps + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
-    uint64_t k = 0; /* next batch of RB rollouts */
-    for (uint64_t j = 0; j < npass; ++j) {
-        nb_sync(bar + (int)(j & 1));
-        const uint64_t avail = ((j + 1) * GW_PASS_STEPS < total_steps) ? (j + 1) * GW_PASS_STEPS : total_steps;
-        for (; k < nbuf; ++k) { /* every batch whose codes pass j completed */
-            const uint64_t r0 = k * RB;
-            const uint32_t live = (uint32_t)((cnt - r0 < RB) ? cnt - r0 : RB);
+    const uint32_t total_steps = cnt * d;
+    const uint32_t npass = (total_steps + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
+    uint32_t r0 = 0;    /* first rollout of the next batch */
+    uint32_t qoff = 0;  /* its first code in the queue: (r0 * d) mod ring_codes, always a batch boundary */
+    uint32_t avail = 0; /* steps generated so far */
+    for (uint32_t j = 0; j < npass; ++j) {
+        bar_sync(pass_bar, 96);
+        avail = (total_steps - avail > (uint32_t)GW_PASS_STEPS) ? avail + GW_PASS_STEPS : total_steps;
+        while (r0 < cnt) { /* every batch whose codes pass j completed */
+            const uint32_t live = (cnt - r0 < RB) ? cnt - r0 : RB;
             if ((r0 + live) * d > avail) break;
-            consume_batch<KIND, CodeT, Q>(P, queue, qmask, tab, first + r0, (uint32_t)((r0 * d) & qmask), live, lane, acc);
-        }
-        if (j + 2 < npass) {
-            __syncwarp();
-            nb_arrive(bar + 2 + (int)(j & 1));
+            consume_batch<KIND, CodeT, Q, TAB_SMEM>(P, queue + qoff, tab, first + r0, live, lane, acc);
+            r0 += RB;
+            qoff += P.bcodes;
+            if (qoff >= P.ring_codes) qoff = 0;
         }
     }
 }
 
 template <int KIND, typename CodeT, bool TAB_SMEM>
-__global__ void __launch_bounds__(GW_PAIRS * 64) k_stream2(const Stream2Params P) {
+__global__ void __launch_bounds__(SP_THREADS) k_stream2(const Stream2Params P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t d = P.depth;
-    /* layout: rings [PAIRS][896] u32 | queues [PAIRS][Q + 16] CodeT | tables */
+    /* layout: rings [SP_STREAMS][896] u32 | queues [SP_STREAMS][ring_codes + 16] CodeT | tables */
     uint32_t *rings = reinterpret_cast<uint32_t *>(smem_raw);
-    CodeT *queues = reinterpret_cast<CodeT *>(rings + GW_PAIRS * GW_RING);
-    const uint32_t Q = P.qlen;
+    CodeT *queues = reinterpret_cast<CodeT *>(rings + SP_STREAMS * GW_RING);
+    const uint32_t R = P.ring_codes;
     const uint8_t *tab = P.tab;
     if (KIND == KIND_TREE && TAB_SMEM) {
-        uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * (Q + 16));
+        uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)SP_STREAMS * (R + 16));
         stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
         const uint32_t bytes = P.tab_len * (P.T > 1 ? 2u : 1u);
         for (uint32_t i = tid; i < bytes; i += blockDim.x) stab[i] = P.tab[i];
         tab = stab;
     }
-    const int pair = warp % GW_PAIRS;
-    const bool is_gen = warp < GW_PAIRS;
-    const uint32_t stream = blockIdx.x * GW_PAIRS + pair;
-    uint32_t *ring = rings + pair * GW_RING;
-    CodeT *queue = queues + (size_t)pair * (Q + 16);
-    /* four named barriers per pair; id 0 doubles as __syncthreads, used only below, before any
-     * pair starts */
-    const int bar = 4 * pair;
-    if (stream < P.streams && is_gen) gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
+    const int sl = warp % SP_STREAMS;   /* stream of this warp within the CTA: its three warps share a sub-partition */
+    const int role = warp / SP_STREAMS; /* 0, 1: generator halves A, B; 2: consumer */
+    const uint32_t stream = blockIdx.x * SP_STREAMS + sl;
+    uint32_t *ring = rings + sl * GW_RING;
+    CodeT *queue = queues + (size_t)sl * (R + 16);
+    const int pair_bar = 1 + sl, pass_bar = 1 + SP_STREAMS + sl; /* barrier 0 is __syncthreads, used once below */
+    if (stream < P.streams && role == 0) gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
     __syncthreads();
     if (stream >= P.streams) return;
 
     const uint64_t first = (uint64_t)stream * P.chunk;
-    const uint64_t cnt = (first + P.chunk <= P.n) ? P.chunk : P.n - first;
-    const uint64_t total_steps = cnt * d;
-    const uint32_t qmask = Q - 1;
+    const uint32_t cnt = (uint32_t)((first + P.chunk <= P.n) ? P.chunk : P.n - first);
+    const uint32_t total_steps = cnt * d;
+    const uint32_t groups = (total_steps + GW_STEPS - 1) / GW_STEPS;
 
-    if (is_gen) {
-        QueueSink<CodeT> sink{queue, qmask, bar, lane};
-        gw_generate(ring, (total_steps + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
+    if (role == 0) {
+        pair_generate<0, CodeT>(ring, queue, R, groups, lane, P.mrow, P.mcol, P.cols, pair_bar, pass_bar);
         if (stream + 1 == P.streams && P.end_window) {
             /* words generated in the current pass before the stream's end: 4 * total_steps mod 896,
              * except that a stream ending exactly on a pass boundary sits at 896 */
-            const uint64_t words = 4 * total_steps;
+            const uint64_t words = 4ull * total_steps;
             uint32_t w_end = (uint32_t)(words % GW_RING);
             if (w_end == 0 && words > 0) w_end = GW_RING;
             gw_dump_window(ring, w_end, P.end_window, lane);
         }
         return;
     }
+    if (role == 1) {
+        pair_generate<1, CodeT>(ring, queue, R, groups, lane, P.mrow, P.mcol, P.cols, pair_bar, pass_bar);
+        return;
+    }
 
     /* ---- consumer warp */
     RolloutAcc acc;
     if (P.rb == 128)
-        consume_stream<KIND, CodeT, 4>(P, queue, qmask, tab, bar, first, cnt, lane, acc);
+        consume_stream<KIND, CodeT, 4, TAB_SMEM>(P, queue, tab, pass_bar, first, cnt, lane, acc);
     else if (P.rb == 64)
-        consume_stream<KIND, CodeT, 2>(P, queue, qmask, tab, bar, first, cnt, lane, acc);
+        consume_stream<KIND, CodeT, 2, TAB_SMEM>(P, queue, tab, pass_bar, first, cnt, lane, acc);
     else
-        consume_stream<KIND, CodeT, 1>(P, queue, qmask, tab, bar, first, cnt, lane, acc);
+        consume_stream<KIND, CodeT, 1, TAB_SMEM>(P, queue, tab, pass_bar, first, cnt, lane, acc);
     if (P.sums) {
-        acc.w = warp_sum_u64(acc.w);
-        acc.d = warp_sum_u64(acc.d);
-        acc.l = warp_sum_u64(acc.l);
-        acc.h = warp_sum_u64(acc.h);
-        acc.n = warp_sum_u64(acc.n);
+        unsigned long long pay_sum = warp_sum_u64(acc.pay_sum), draws = warp_sum_u64(acc.draws), n = warp_sum_u64(acc.n);
+        const unsigned long long h = warp_sum_u64(acc.h);
         if (lane == 0) {
-            if (acc.w) atomicAdd(P.sums + 0, acc.w);
-            if (acc.d) atomicAdd(P.sums + 1, acc.d);
-            if (acc.l) atomicAdd(P.sums + 2, acc.l);
-            atomicAdd(P.sums + 3, acc.n * d);
-            atomicAdd(P.sums + 4, acc.h);
+            if (KIND == KIND_MOLD) { /* MoldState never writes a payoff: every rollout counts in the draw slot */
+                atomicAdd(P.sums + 1, n);
+            } else {
+                const unsigned long long wins = (pay_sum - draws) / 2; /* payoff_x2 2 = row win, 1 = draw, 0 = loss */
+                if (wins) atomicAdd(P.sums + 0, wins);
+                if (draws) atomicAdd(P.sums + 1, draws);
+                if (n - wins - draws) atomicAdd(P.sums + 2, n - wins - draws);
+            }
+            atomicAdd(P.sums + 3, n * d);
+            atomicAdd(P.sums + 4, h);
         }
     }
 }
