@@ -85,12 +85,14 @@ __device__ __forceinline__ void ja_nibble(uint32_t (&acc)[JA_OUT], const uint32_
 
 __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
     k_jump_apply(const uint32_t *__restrict__ ext, const uint32_t *__restrict__ polys, uint32_t splits, uint32_t *d_ck,
-                 uint32_t skip) {
+                 uint32_t skip, uint32_t pstep, uint32_t regular, uint32_t extra_rel) {
     extern __shared__ __align__(16) uint32_t ja_smem[];
     uint32_t *sext = ja_smem;
     uint32_t *spoly = ja_smem + JA_EXT_WORDS;
     uint32_t *sred = spoly + MTJ_POLY_WORDS;
-    const uint32_t c = blockIdx.x / splits + skip, sp = blockIdx.x % splits; /* bitmap c of the family -> window c */
+    /* window c <- bitmap c * pstep of the family (the one window behind the regular ones: bitmap extra_rel) */
+    const uint32_t c = blockIdx.x / splits + skip, sp = blockIdx.x % splits;
+    const uint32_t pc = c < regular ? c * pstep : extra_rel;
     const int tid = threadIdx.x;
     const uint32_t cta_lo = MTJ_POLY_WORDS * sp / splits, cta_hi = MTJ_POLY_WORDS * (sp + 1) / splits;
     {
@@ -99,8 +101,8 @@ __global__ void __launch_bounds__(JA_SEGS *JA_SEG_THREADS, 2)
         const uint4 *src = reinterpret_cast<const uint4 *>(ext);
         uint4 *dst = reinterpret_cast<uint4 *>(sext);
         for (int i = q_lo + tid; i < q_hi; i += JA_SEGS * JA_SEG_THREADS) dst[i] = src[i];
-        const uint32_t *pc = polys + (size_t)c * MTJ_POLY_WORDS;
-        for (int i = cta_lo + tid; i < (int)cta_hi; i += JA_SEGS * JA_SEG_THREADS) spoly[i] = pc[i];
+        const uint32_t *pp = polys + (size_t)pc * MTJ_POLY_WORDS;
+        for (int i = cta_lo + tid; i < (int)cta_hi; i += JA_SEGS * JA_SEG_THREADS) spoly[i] = pp[i];
     }
     __syncthreads();
     const int seg = tid / JA_SEG_THREADS, t = tid % JA_SEG_THREADS;
@@ -215,21 +217,29 @@ static int family_on_device(MtJump &J, cudaStream_t stream, uint64_t first, uint
     return 0;
 }
 
-int MtJump::prepare(cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride, std::string *err) {
-    if (first == 0 && count <= 1) return 0;
+/* Bitmaps a run over (first, count, pstep, extra) touches: first .. the largest index it applies. */
+static uint64_t family_span(uint64_t first, uint64_t count, uint64_t pstep, int64_t extra) {
+    uint64_t hi = first + (count ? (count - 1) * pstep : 0);
+    if (extra >= 0) hi = std::max<uint64_t>(hi, (uint64_t)extra);
+    return hi - first + 1;
+}
+
+int MtJump::prepare(cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride, std::string *err, uint64_t pstep,
+                    int64_t extra) {
+    if (first == 0 && count <= 1 && extra < 0) return 0;
     DevFamily *fam = nullptr;
-    return family_on_device(*this, stream, first, count, stride, &fam, err);
+    return family_on_device(*this, stream, first, family_span(first, count, pstep, extra), stride, &fam, err);
 }
 
 int MtJump::run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t first, uint64_t count, uint64_t stride,
-                uint32_t *d_ck, uint64_t *launches, std::string *err) {
-    if (first == 0 && count <= 1) {
+                uint32_t *d_ck, uint64_t *launches, std::string *err, uint64_t pstep, int64_t extra) {
+    if (first == 0 && count <= 1 && extra < 0) {
         JCU(cudaMemcpyAsync(d_ck, base_window, sizeof(uint32_t) * MT_N, cudaMemcpyHostToDevice, stream));
         last_build_ms = 0;
         return 0;
     }
     DevFamily *fam = nullptr;
-    if (family_on_device(*this, stream, first, count, stride, &fam, err)) return -1;
+    if (family_on_device(*this, stream, first, family_span(first, count, pstep, extra), stride, &fam, err)) return -1;
     if (!d_ext) {
         JCU(cudaMalloc(&d_ext, sizeof(uint32_t) * (MTJ_EXT_LEN + MT_N)));
         JCU(cudaFuncSetAttribute(k_jump_apply, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)JA_SMEM));
@@ -237,14 +247,20 @@ int MtJump::run(cudaStream_t stream, int sms, const uint32_t *base_window, uint6
     uint32_t *d_base = d_ext + MTJ_EXT_LEN;
     JCU(cudaMemcpyAsync(d_base, base_window, sizeof(uint32_t) * MT_N, cudaMemcpyHostToDevice, stream));
     const uint32_t skip = first == 0 ? 1u : 0u; /* window 0 of an unsharded batch needs no polynomial */
-    const uint64_t apply = count - skip;
+    const uint64_t windows = count + (extra >= 0 ? 1 : 0);
+    const uint64_t apply = windows - skip;
+    if (apply == 0) { /* a single window which is the base itself */
+        JCU(cudaMemcpyAsync(d_ck, base_window, sizeof(uint32_t) * MT_N, cudaMemcpyHostToDevice, stream));
+        return 0;
+    }
     /* few checkpoints: split each polynomial over several CTAs so the launch still fills the GPU */
     uint64_t splits = (2ull * sms + apply - 1) / apply;
     splits = std::max<uint64_t>(1, std::min<uint64_t>(splits, 13));
     if (splits > 1) JCU(cudaMemsetAsync(d_ck + (size_t)MT_N * skip, 0, sizeof(uint32_t) * MT_N * apply, stream));
     k_jump_extend<<<1, GEN_THREADS, 0, stream>>>(d_base, d_ext, skip ? d_ck : nullptr);
-    k_jump_apply<<<(unsigned)(apply * splits), JA_SEGS * JA_SEG_THREADS, JA_SMEM, stream>>>(d_ext, fam->bits, (uint32_t)splits,
-                                                                                         d_ck, skip);
+    k_jump_apply<<<(unsigned)(apply * splits), JA_SEGS * JA_SEG_THREADS, JA_SMEM, stream>>>(
+        d_ext, fam->bits, (uint32_t)splits, d_ck, skip, (uint32_t)pstep, (uint32_t)count,
+        extra >= 0 ? (uint32_t)((uint64_t)extra - first) : 0u);
     if (launches) *launches += 2;
     JCU(cudaGetLastError());
     return 0;

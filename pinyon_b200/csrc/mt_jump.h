@@ -59,9 +59,13 @@ struct MtJump {
      * sharded batch takes its slice of the global checkpoint family without any host-side jump.
      * base_window must stay valid until the stream has consumed it (pinned staging memory).
      * Asynchronous on `stream` unless a family has to be built. */
+    /* pstep / extra: the fused kernel pairs a forward and a backward stream around one window, so it wants windows at
+     * every SECOND stream position only — window j at (first + pstep * j) * stride — plus, when the batch's last
+     * stream has an odd index, one more (stored behind the regular ones) at position extra * stride. */
     int run(cudaStream_t stream, int sms, const uint32_t *base_window, uint64_t first, uint64_t count, uint64_t stride,
-            uint32_t *d_ck, uint64_t *launches, std::string *err);
+            uint32_t *d_ck, uint64_t *launches, std::string *err, uint64_t pstep = 1, int64_t extra = -1);
     /* Build and upload the family now (pcu_warmup): the ~80 ms of GF(2) arithmetic a new stride costs. */
-    int prepare(cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride, std::string *err);
+    int prepare(cudaStream_t stream, uint64_t first, uint64_t count, uint64_t stride, std::string *err, uint64_t pstep = 1,
+                int64_t extra = -1);
     void release();
 };

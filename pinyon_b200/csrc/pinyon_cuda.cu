@@ -77,6 +77,7 @@ struct pcu_ctx {
     std::string path;
     uint64_t launches = 0;
     int streams_per_sm = 0; /* model streams (generator warps) resident per SM; 0 = by batch size (run_stream) */
+    double dense_streams_from = 5e7; /* rollout-steps per call from which 8 streams per SM pay for their checkpoints */
     int force_general = 0;
     int rb = 32;        /* rollouts per consumer batch of the fused kernels (32 or 64) */
     int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
@@ -534,29 +535,43 @@ int finish_all(pcu_ctx *ctx, const pcu_out *out, uint64_t n, const OutDev &od, p
 
 /* ------------------------------------------------ model-stream checkpoints */
 
-/* Fill B_CKPT with `count` windows: window c holds the 624 raw words preceding model
- * draw number c * stride, counted from the engine's next draw. */
-int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t first, uint64_t count, uint64_t stride) {
+/* Fill B_CKPT with windows: window j (j < count) holds the 624 raw words preceding model draw number
+ * (first + pstep * j) * stride, counted from the engine's next draw; with extra >= 0 one more window, behind them,
+ * at draw extra * stride (see MtJump::run). */
+int make_checkpoints(pcu_ctx *ctx, const uint32_t *mt_x, uint32_t mt_p, uint64_t first, uint64_t count, uint64_t stride,
+                     uint64_t pstep = 1, int64_t extra = -1) {
     uint32_t *win = ctx->pin_small + PIN_BASE_WINDOW; /* pinned: the upload below needs no host sync */
     host_window_from_engine(mt_x, mt_p, win);
-    CU(ctx->buf[B_CKPT].ensure(sizeof(uint32_t) * MT_N * (count + 1)));
+    const uint64_t windows = count + (extra >= 0 ? 1 : 0);
+    CU(ctx->buf[B_CKPT].ensure(sizeof(uint32_t) * MT_N * (windows + 1)));
     CU(ctx->buf[B_ENDWIN].ensure(sizeof(uint32_t) * MT_N));
     uint32_t *d_ck = reinterpret_cast<uint32_t *>(ctx->buf[B_CKPT].p);
-    if (ctx->host_checkpoints && (count > 1 || first > 0)) {
+    if (ctx->host_checkpoints && (windows > 1 || first > 0)) {
         /* test hook: plain stepping on the host, the definition the jump kernels must match */
-        std::vector<uint32_t> all((size_t)MT_N * count);
+        std::vector<uint32_t> all((size_t)MT_N * windows);
         std::vector<uint32_t> w(win, win + MT_N);
-        for (uint64_t c = 0; c < first; ++c) host_window_advance(w.data(), stride);
+        uint64_t at = 0; /* position of w in units of stride */
+        auto advance_to = [&](uint64_t pos) {
+            for (; at < pos; ++at) host_window_advance(w.data(), stride);
+        };
         for (uint64_t c = 0; c < count; ++c) {
+            advance_to(first + pstep * c);
             memcpy(all.data() + (size_t)MT_N * c, w.data(), sizeof(uint32_t) * MT_N);
-            if (c + 1 < count) host_window_advance(w.data(), stride);
         }
-        CU(cudaMemcpyAsync(d_ck, all.data(), sizeof(uint32_t) * MT_N * count, cudaMemcpyHostToDevice, ctx->stream));
+        if (extra >= 0) {
+            if ((uint64_t)extra < at) { /* behind the last regular window: start over */
+                w.assign(win, win + MT_N);
+                at = 0;
+            }
+            advance_to((uint64_t)extra);
+            memcpy(all.data() + (size_t)MT_N * count, w.data(), sizeof(uint32_t) * MT_N);
+        }
+        CU(cudaMemcpyAsync(d_ck, all.data(), sizeof(uint32_t) * MT_N * windows, cudaMemcpyHostToDevice, ctx->stream));
         CU(cudaStreamSynchronize(ctx->stream)); /* `all` is pageable and about to go out of scope */
         return PCU_OK;
     }
     std::string jerr;
-    if (ctx->jump.run(ctx->stream, ctx->sms, win, first, count, stride, d_ck, &ctx->launches, &jerr) != 0)
+    if (ctx->jump.run(ctx->stream, ctx->sms, win, first, count, stride, d_ck, &ctx->launches, &jerr, pstep, extra) != 0)
         return fail(ctx, PCU_ERR_CUDA, "jump-ahead failed: %s", jerr.c_str());
     ctx->last_family_ms += ctx->jump.last_build_ms;
     return PCU_OK;
@@ -602,9 +617,9 @@ template <int KIND, typename CodeT>
 int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t smem) {
     auto kern = tab_smem ? k_stream2<KIND, CodeT, true> : k_stream2<KIND, CodeT, false>;
     CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned ctas = (P.streams + SP_STREAMS - 1) / SP_STREAMS;
+    const unsigned ctas = (P.streams + GW_PAIRS - 1) / GW_PAIRS;
     CU(cudaEventRecord(ctx->ev0, ctx->stream));
-    kern<<<ctas, SP_THREADS, smem, ctx->stream>>>(P);
+    kern<<<ctas, GW_PAIRS * 64, smem, ctx->stream>>>(P);
     CU(cudaEventRecord(ctx->ev1, ctx->stream));
     ctx->ev_valid = true;
     ctx->launches++;
@@ -615,10 +630,10 @@ int launch_stream(pcu_ctx *ctx, const Stream2Params &P, bool tab_smem, size_t sm
 constexpr size_t SMEM_LIMIT = 200 * 1024;
 
 /* Code queue of one stream: a whole number of batches (so a batch never wraps), holding a batch plus the pass being
- * consumed and the pass being generated. */
+ * consumed, the pass being generated and the 156 window steps a backward stream starts with. */
 uint32_t stream_ring_codes(uint32_t rb, uint32_t depth) {
     const uint64_t b = (uint64_t)rb * depth;
-    const uint64_t slots = 2 + (2 * GW_PASS_STEPS + b - 1) / b;
+    const uint64_t slots = 2 + (2 * GW_PASS_STEPS + GW_WINDOW_STEPS + b - 1) / b;
     return (uint32_t)std::min<uint64_t>(slots * b, 0xffffffffull);
 }
 
@@ -626,16 +641,16 @@ uint32_t stream_ring_codes(uint32_t rb, uint32_t depth) {
  * (codes through HBM). */
 bool stream_fits(uint32_t depth, uint64_t actions, uint32_t rb = 32) {
     const uint64_t ring = (uint64_t)stream_ring_codes(rb, depth);
-    const size_t smem = (size_t)SP_STREAMS * GW_RING * 4 + (size_t)SP_STREAMS * (ring + 16) * (actions <= 256 ? 1 : 2) + 16;
+    const size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + (size_t)GW_PAIRS * (ring + 16) * (actions <= 256 ? 1 : 2) + 16;
     return smem <= SMEM_LIMIT;
 }
 
-/* Model streams (generator warps) resident per SM for a uniform-depth batch of n rollouts on this GPU.  Every
- * stream costs one jump-ahead checkpoint (~0.5 us of the whole GPU) and a second generator warp per scheduler
- * hides the first one's fixed-latency stalls: worth it from ~2.5e8 rollout-steps per call on
- * (tools/sweep_stream.py: config B 2.78 -> 2.52 ms at 8 per SM, config A 1.41 -> 1.53 ms). */
+/* Model streams (generator warps) resident per SM for a uniform-depth batch of n rollouts on this GPU.  A PAIR of
+ * streams costs one jump-ahead checkpoint (~0.4 us of the whole GPU: one runs forwards from it, one backwards) and a
+ * second generator warp per scheduler hides the first one's fixed-latency stalls: worth it from ~5e7 rollout-steps
+ * per call on (option "dense_streams_from"; tools/sweep_stream.py). */
 int streams_per_sm_for(const pcu_ctx *ctx, uint64_t n, uint32_t depth) {
-    return ctx->streams_per_sm ? ctx->streams_per_sm : ((double)n * depth >= 2.5e8 ? 8 : 4);
+    return ctx->streams_per_sm ? ctx->streams_per_sm : ((double)n * depth >= ctx->dense_streams_from ? 8 : 4);
 }
 
 /* Fused path (mode S, uniform depth, shared or absent state stream). */
@@ -658,7 +673,11 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.ring_codes = stream_ring_codes(P.rb, P.depth);
     if (P.chunk * (uint64_t)P.depth >= (1ull << 32))
         return fail(ctx, PCU_ERR_UNSUPPORTED, "a model stream of %llu x %u steps exceeds 2^32", (unsigned long long)P.chunk, P.depth);
-    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, first_stream, P.streams, 4ull * P.depth * P.chunk);
+    /* one window per PAIR of streams: even stream 2c runs forwards from it, odd stream 2c - 1 backwards; an odd-indexed
+     * last stream runs forwards from a window of its own */
+    P.ck_regular = (P.streams + 1) / 2;
+    const int64_t extra = (P.streams % 2 == 0) ? (int64_t)(first_stream + P.streams - 1) : -1;
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, first_stream, P.ck_regular, 4ull * P.depth * P.chunk, 2, extra);
     if (rc) return rc;
     P.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
     const bool want_end = !ctx->hint.active || ctx->hint.last;
@@ -671,8 +690,8 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.vec_ok = (P.chunk % 4 == 0) && ((uintptr_t)od.payoff % 4 == 0) && ((uintptr_t)od.hash % 16 == 0);
     (void)out;
     const bool code8 = (uint64_t)rows * P.cols <= 256;
-    const size_t queue_bytes = (size_t)SP_STREAMS * (P.ring_codes + 16) * (code8 ? 1 : 2);
-    size_t smem = (size_t)SP_STREAMS * GW_RING * 4 + queue_bytes + 16;
+    const size_t queue_bytes = (size_t)GW_PAIRS * (P.ring_codes + 16) * (code8 ? 1 : 2);
+    size_t smem = (size_t)GW_PAIRS * GW_RING * 4 + queue_bytes + 16;
     const size_t tab_bytes = (size_t)P.tab_len * (P.T > 1 ? 2 : 1);
     bool tab_smem = false;
     if (KIND == KIND_TREE && smem + tab_bytes + 16 <= SMEM_LIMIT) {
@@ -1798,7 +1817,9 @@ void plan_shards(const Multi &M, uint64_t n, int mode, const uint16_t *depth, ui
         for (const pcu_ctx *k : M.kids) slots += (uint64_t)k->sms * streams_per_sm_for(k0, n / G, depth_u);
         const uint64_t min_chunk = std::max<uint64_t>(128, (4096 + depth_u - 1) / std::max<uint32_t>(depth_u, 1));
         const uint64_t chunk = pick_rollout_chunk(n, slots, min_chunk);
-        const uint64_t S = (n + chunk - 1) / chunk, spg = (S + G - 1) / G;
+        const uint64_t S = (n + chunk - 1) / chunk;
+        uint64_t spg = (S + G - 1) / G;
+        spg += spg & 1; /* whole forward/backward stream pairs per GPU */
         *chunk_out = chunk;
         for (size_t g = 0; g < G; ++g) {
             const uint64_t s0 = std::min<uint64_t>(S, g * spg), s1 = std::min<uint64_t>(S, s0 + spg);
@@ -2142,14 +2163,17 @@ int pcu_warmup(pcu_ctx *ctx, uint64_t n, uint32_t depth) {
             pcu_ctx *kid = M.kids[g];
             cudaSetDevice(kid->device);
             const uint64_t streams = (plan[g].count + chunk - 1) / chunk;
-            if (kid->jump.prepare(kid->stream, plan[g].first_stream, streams, 4ull * depth * chunk, &jerr))
+            const int64_t extra = streams % 2 == 0 ? (int64_t)(plan[g].first_stream + streams - 1) : -1;
+            if (kid->jump.prepare(kid->stream, plan[g].first_stream, (streams + 1) / 2, 4ull * depth * chunk, &jerr, 2, extra))
                 return fail(ctx, PCU_ERR_CUDA, "warm-up failed: %s", jerr.c_str());
         }
         return PCU_OK;
     }
     CU(cudaSetDevice(ctx->device));
     const uint64_t chunk = pick_rollout_chunk(n, (uint64_t)ctx->sms * streams_per_sm_for(ctx, n, depth), 128);
-    if (ctx->jump.prepare(ctx->stream, 0, (n + chunk - 1) / chunk, 4ull * depth * chunk, &jerr))
+    const uint64_t streams = (n + chunk - 1) / chunk;
+    if (ctx->jump.prepare(ctx->stream, 0, (streams + 1) / 2, 4ull * depth * chunk, &jerr, 2,
+                          streams % 2 == 0 ? (int64_t)(streams - 1) : -1))
         return fail(ctx, PCU_ERR_CUDA, "warm-up failed: %s", jerr.c_str());
     return PCU_OK;
 }

@@ -11,12 +11,13 @@
 //     word first, random.hh:26,28) live in one thread: no shuffles, no redundant lanes;
 //   - no CTA barrier anywhere: a group ends with __syncwarp().
 //
-// Fused kernel (k_stream2): CTA = SP_STREAMS streams x 3 warps.  Two generator warps share a
-// stream and alternate its 224-word groups (the recurrence of one group runs beside the
-// tempering of the previous one); they put joint action codes (row * cols + col) into a
-// shared-memory queue, and the stream's consumer warp plays the rollouts whose codes are
-// complete, one to four per lane, against the shared state-stream table.  Hand-off is by named
-// barriers (bar.sync): a waiting warp takes no issue slots.
+// Fused kernel (k_stream2): CTA = GW_PAIRS generator warps + GW_PAIRS consumer warps.
+// Generator g streams joint action codes (row * cols + col) into a shared-memory queue;
+// consumer g (same SM sub-partition: warp id + GW_PAIRS) plays the rollouts whose codes are
+// complete, one to four per lane, against the shared state-stream table.  Streams come in
+// pairs around one jump-ahead checkpoint, one generated forwards and one BACKWARDS from it.
+// Hand-off is by named barriers (bar.sync / bar.arrive, 64 threads), so the consumer's
+// latency-bound table walks overlap the generator's ALU work on the same scheduler.
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -97,6 +98,74 @@ __device__ __forceinline__ void gw_load_window(uint32_t *ring, const uint32_t *c
     for (int i = lane; i < MT_N; i += 32) ring[48 + i] = ckpt[i];
 }
 
+/* ---- the same stream generated BACKWARDS.
+ * MT19937 is invertible: from X[n] ^ X[n-227] = (y >> 1) ^ (lsb(y) ? 0x9908b0df : 0), y = msb(X[n-624]) | low31(X[n-623]),
+ * the top bit of the left side is lsb(y) (the constant has its top bit set, y >> 1 has not) and bit 30 is msb(y) (the
+ * constant's bit 30 is clear).  So a window also yields the words BEFORE it, and ONE jump-ahead checkpoint serves TWO
+ * model streams: one generated forwards from it, one backwards — half the polynomial applications per stream.
+ * In reversed indexing Z[i] = X[P - 1 - i] (Z[0..623] is the window, newest word first) the inverse is again a forward
+ * recurrence,  Z[j] = G(Z[j-624], Z[j-623], Z[j-397], Z[j-396])  for j >= 624:
+ *     v1 = Z[j-624] ^ Z[j-397]     msb(Z[j])   = bit 30 of v1
+ *     v2 = Z[j-623] ^ Z[j-396]     low31(Z[j]) = low31(((v2 ^ (msb(v2) ? 0x9908b0df : 0)) << 1) | msb(v2))
+ * with the SAME ring layout as the forward generator (word n' of the current pass in slot (n' + 672) mod 896, the
+ * window in slots 48..671) and a shortest lag of 396 words, so 224-word groups are independent of their predecessor.
+ * v2 of word j is v1 of word j + 1: five XORs serve a lane's four consecutive words. */
+template <int PH>
+__device__ __forceinline__ void gw_load_b(const uint32_t *ring, int l4, GwOps &o, uint4 &d0, uint4 &d1) {
+    constexpr int off0 = GW_WORDS * PH, off1 = off0 + GW_WORDS / 2;
+    o.a0 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off0 + 48>(l4)); /* Z[j-624 .. j-621] */
+    o.a1 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off1 + 48>(l4));
+    o.a04 = ring[gw_slot<off0 + 52>(l4)];                                    /* Z[j-620] */
+    o.a14 = ring[gw_slot<off1 + 52>(l4)];
+    o.c0 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off0 + 272>(l4)); /* Z[j-400 .. j-397]: .w is Z[j-397] */
+    o.c1 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off1 + 272>(l4));
+    d0 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off0 + 276>(l4));   /* Z[j-396 .. j-393] */
+    d1 = *reinterpret_cast<const uint4 *>(ring + gw_slot<off1 + 276>(l4));
+}
+
+__device__ __forceinline__ uint32_t mt_untwist_dev(uint32_t v1, uint32_t v2) {
+    const uint32_t sgn = (uint32_t)((int32_t)v2 >> 31);
+    uint32_t w, x;
+    asm("lop3.b32 %0, %1, %2, %3, 0x78;" : "=r"(w) : "r"(v2), "r"(sgn), "r"(0x9908b0dfu)); /* v2 ^ (sgn & matrix) */
+    const uint32_t y = __funnelshift_l(v2, w, 1);                                            /* (w << 1) | msb(v2) */
+    asm("lop3.b32 %0, %1, %2, %3, 0xE4;" : "=r"(x) : "r"(v1 << 1), "r"(y), "r"(0x80000000u)); /* msb from v1's bit 30 */
+    return x;
+}
+
+__device__ __forceinline__ uint4 gw_untwist4(const uint4 &a, uint32_t a4, uint32_t c3, const uint4 &d) {
+    /* V[k] = Z[j-624+k] ^ Z[j-397+k], k = 0..4 */
+    const uint32_t v0 = a.x ^ c3, v1 = a.y ^ d.x, v2 = a.z ^ d.y, v3 = a.w ^ d.z, v4 = a4 ^ d.w;
+    uint4 x;
+    x.x = mt_untwist_dev(v0, v1);
+    x.y = mt_untwist_dev(v1, v2);
+    x.z = mt_untwist_dev(v2, v3);
+    x.w = mt_untwist_dev(v3, v4);
+    return x;
+}
+
+/* A backward lane holds its step's words newest-index first: (w3, w2, w1, w0). */
+__device__ __forceinline__ uint32_t gw_code_b(const uint4 &x, const FoldConst &mrow, const FoldConst &mcol, uint32_t cols) {
+    const uint32_t row = mod64_fold(mt_temper(x.w), mt_temper(x.z), mrow);
+    const uint32_t col = mod64_fold(mt_temper(x.y), mt_temper(x.x), mcol);
+    return row * cols + col;
+}
+
+/* Z[i] = window[623 - i] into slots 48..671.
+ * The low 31 bits of a window's OLDEST word are not part of the generator's 19937-bit state (the forward recurrence
+ * reads only its top bit), and the jump-ahead does not reproduce them: x^D = g(x) mod phi holds for the state, and the
+ * polynomial's constant term drags the equally dead bits of the base window's oldest word into them.  Generating
+ * backwards DOES read them, so they are rebuilt here from the window itself by the inverse recurrence:
+ * low31(X[m]) comes from X[m+623] ^ X[m+396], i.e. low31(Z[623]) from Z[0] ^ Z[227]. */
+__device__ __forceinline__ void gw_load_window_b(uint32_t *ring, const uint32_t *ckpt, int lane) {
+    for (int i = lane; i < MT_N; i += 32) ring[48 + i] = ckpt[MT_N - 1 - i];
+    __syncwarp();
+    if (lane == 0) {
+        const uint32_t old = ring[48 + MT_N - 1];
+        ring[48 + MT_N - 1] = mt_untwist_dev(old >> 1, ring[48] ^ ring[48 + MT_LAG]); /* keeps old's top bit */
+    }
+    __syncwarp();
+}
+
 /* The 624 raw words preceding stream word `w_end` of the current 896-word pass. */
 __device__ __forceinline__ void gw_dump_window(const uint32_t *ring, uint32_t w_end, uint32_t *dst, int lane) {
     for (int i = lane; i < MT_N; i += 32) dst[i] = ring[(w_end + 48 + i) % GW_RING];
@@ -110,32 +179,47 @@ __device__ __forceinline__ void gw_dump_window(const uint32_t *ring, uint32_t w_
  *   sink.put(g, c0, c1, active)   codes of steps 56 g + lane and 56 g + 28 + lane
  *   sink.end_pass(j)              after the last group of pass j (publishes progress)
  * Lanes 28..31 shadow lane 27 (same loads, stores predicated off): no divergence. */
-template <typename Sink>
+template <int DIR, typename Sink>
 __device__ __forceinline__ void gw_generate(uint32_t *ring, uint64_t groups, int lane, const FoldConst &mrow,
                                             const FoldConst &mcol, uint32_t cols, Sink &sink) {
     const bool active = lane < GW_ACTIVE;
     const int l4 = 4 * (active ? lane : GW_ACTIVE - 1);
     if (groups == 0) return;
     GwOps o;
-    uint4 x0, x1;
-    gw_load<0>(ring, l4, o);
-    x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);
-    x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);
+    uint4 d0, d1, x0, x1;
+#define GW_LOAD(PH)                                     \
+    {                                                   \
+        if (DIR == 0)                                   \
+            gw_load<(PH)>(ring, l4, o);                 \
+        else                                            \
+            gw_load_b<(PH)>(ring, l4, o, d0, d1);       \
+    }
+#define GW_TWIST()                                             \
+    {                                                          \
+        if (DIR == 0) {                                        \
+            x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);          \
+            x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);          \
+        } else {                                               \
+            x0 = gw_untwist4(o.a0, o.a04, o.c0.w, d0);         \
+            x1 = gw_untwist4(o.a1, o.a14, o.c1.w, d1);         \
+        }                                                      \
+    }
+    GW_LOAD(0)
+    GW_TWIST()
     gw_store<0>(ring, l4, active, x0, x1);
     __syncwarp();
 
-#define GW_BODY(PH, NEXT)                                                  \
-    {                                                                      \
-        if (NEXT) gw_load<((PH) + 1) & 3>(ring, l4, o);                    \
-        const uint32_t c0 = gw_code(x0, mrow, mcol, cols);                 \
-        const uint32_t c1 = gw_code(x1, mrow, mcol, cols);                 \
-        sink.put(g + (PH), c0, c1, active);                                \
-        if (NEXT) {                                                        \
-            x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);                      \
-            x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);                      \
-            gw_store<((PH) + 1) & 3>(ring, l4, active, x0, x1);            \
-            __syncwarp();                                                  \
-        }                                                                  \
+#define GW_BODY(PH, NEXT)                                                                                  \
+    {                                                                                                      \
+        if (NEXT) GW_LOAD(((PH) + 1) & 3)                                                                  \
+        const uint32_t c0 = DIR == 0 ? gw_code(x0, mrow, mcol, cols) : gw_code_b(x0, mrow, mcol, cols);    \
+        const uint32_t c1 = DIR == 0 ? gw_code(x1, mrow, mcol, cols) : gw_code_b(x1, mrow, mcol, cols);    \
+        sink.put(g + (PH), c0, c1, active);                                                                \
+        if (NEXT) {                                                                                        \
+            GW_TWIST()                                                                                     \
+            gw_store<((PH) + 1) & 3>(ring, l4, active, x0, x1);                                            \
+            __syncwarp();                                                                                  \
+        }                                                                                                  \
     }
 
     uint64_t g = 0, pass = 0;
@@ -155,6 +239,8 @@ __device__ __forceinline__ void gw_generate(uint32_t *ring, uint64_t groups, int
     if (rest > 3) GW_BODY(3, false)
     sink.end_pass(pass);
 #undef GW_BODY
+#undef GW_LOAD
+#undef GW_TWIST
 }
 
 /* ----------------------------------------------------------------- fused kernel */
@@ -163,13 +249,15 @@ struct Stream2Params {
     uint64_t n;       /* rollouts */
     uint64_t chunk;   /* rollouts per stream */
     uint32_t streams; /* ceil(n / chunk) */
+    uint32_t ck_regular; /* windows at even stream positions: (streams + 1) / 2; one extra follows when streams is even */
     uint32_t depth;   /* uniform depth_bound / max_depth */
     uint32_t rb;      /* rollouts per consumer batch: 32, 64 or 128 */
     uint32_t bcodes;  /* rb * depth: codes of one batch */
-    uint32_t ring_codes; /* code queue length: a whole number of batches, >= bcodes + 2 passes */
+    uint32_t ring_codes; /* code queue length: a whole number of batches, >= bcodes + 2 passes + 156 */
     uint32_t cols, T, gen_words;
     FoldConst mrow, mcol;
-    const uint32_t *checkpoints; /* [streams][624] raw words preceding each stream's first model word */
+    const uint32_t *checkpoints; /* [ck_regular (+ 1)][624]: window k holds the raw words preceding model word
+                                    2 k * (4 * depth * chunk); the extra one those preceding the last stream */
     const uint8_t *tab;          /* [tab_len] int8 bias steps, then (T > 1) [tab_len] chance actions; see
                                     host_build_table */
     uint32_t tab_base, tab_len;
@@ -187,34 +275,41 @@ struct Stream2Params {
     uint32_t *end_window; /* [624] raw words preceding the first model word after the batch */
 };
 
-/* One model stream = THREE warps on one SM sub-partition (warp ids s, 4 + s, 8 + s of the CTA):
- *   generator halves A and B   share the stream's 896-word ring and alternate its 224-word groups: A makes groups
- *        0, 2, 4, ..., B groups 1, 3, 5, ...  A group is (1) the recurrence — operands from the ring, twist, store —
- *        and (2) temper + uniform_int reduction of its eight words per lane to two joint action codes, pure register
- *        arithmetic.  Group g + 1 needs group g's words (X[n-227]), so part (1) is a serial chain through the ring;
- *        part (2) is three quarters of the instructions and depends on nothing.  After storing its group a half meets
- *        its partner at a named barrier (64 threads) and then does part (2) WHILE the partner runs part (1) of the next
- *        group: the scheduler always has an independent instruction stream beside the serial one, which one
- *        generator warp per stream did not give it (r1 ncu: one warp issued every 2.4 cycles, ALU pipe 62 % busy),
- *        and a second STREAM per scheduler would cost a second jump-ahead checkpoint.
- *   consumer                    plays the rollouts whose codes are complete, once per pass.
- * Hand-off generator -> consumer: ONE named barrier per stream and pass (96 threads).  The consumer plays the
- * batches completed by pass j while the halves generate pass j + 1; the code queue holds a batch plus two passes. */
-constexpr int SP_STREAMS = 4;               /* streams per CTA */
-constexpr int SP_THREADS = SP_STREAMS * 96; /* 12 warps */
+/* Fused kernel: CTA = GW_PAIRS generator warps + GW_PAIRS consumer warps; generator g and consumer g (warp id
+ * g + GW_PAIRS: the same SM sub-partition) serve one model stream.  Streams come in PAIRS around one jump-ahead
+ * checkpoint: stream 2c runs FORWARDS from the window at position 2c * stride, stream 2c - 1 BACKWARDS from the same
+ * window (gw_load_b / gw_untwist4), so S streams cost S / 2 polynomial applications.  The last stream of a batch is
+ * always a forward one (the only stream that may be shorter than a chunk, and the one that hands back the post-batch
+ * engine window); when its index is odd it gets a checkpoint of its own. */
+constexpr int GW_PAIRS = 4;                    /* generator/consumer warp pairs per CTA */
+constexpr int GW_WINDOW_STEPS = MT_N / 4;      /* 156: the model steps a window itself holds (a backward stream's first) */
 
-__device__ __forceinline__ void bar_sync(int id, int threads) {
-    asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+/* Named barriers between a generator warp and its consumer warp (64 threads each): a waiting
+ * warp takes no issue slots, unlike a polling loop on the same scheduler. */
+__device__ __forceinline__ void nb_sync(int id) { asm volatile("bar.sync %0, 64;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void nb_arrive(int id) {
+    __threadfence_block();
+    asm volatile("bar.arrive %0, 64;" ::"r"(id) : "memory");
 }
 
-/* Joint action codes of one group into the stream's code queue: a ring of `ring_codes` codes indexed by the absolute
- * step number modulo its length.  Lane l holds steps 56 g + l and 56 g + 28 + l. */
+/* Code queue between a generator warp and its consumer: a ring of `ring_codes` codes (a whole number of batches, so a
+ * batch never wraps) indexed by the step number in GENERATION order.  Hand-off is per pass (224 codes) over four named
+ * barriers, full[2] = bar + {0,1} and empty[2] = bar + {2,3}, indexed by pass parity: the generator arrives on
+ * full[j & 1] after pass j and, from pass 2 on, first waits on empty[j & 1], which the consumer arrives on once it has
+ * played every rollout completed by pass j - 2.  Unplayed codes are then less than one batch plus two passes (plus the
+ * 156 codes a backward stream takes from its window before pass 0). */
 template <typename CodeT>
-struct PairQueue {
+struct QueueSink {
     CodeT *queue;
     uint32_t ring_codes;
-    uint32_t qpos; /* (56 g) mod ring_codes for this half's next group */
-    __device__ __forceinline__ void put(uint32_t c0, uint32_t c1, int lane, bool active) {
+    int bar;
+    int lane;
+    uint32_t qpos; /* queue slot of the next group's first code */
+
+    __device__ __forceinline__ void begin_pass(uint64_t pass) {
+        if (pass >= 2) nb_sync(bar + 2 + (int)(pass & 1));
+    }
+    __device__ __forceinline__ void put(uint64_t, uint32_t c0, uint32_t c1, bool active) {
         uint32_t i0 = qpos + lane, i1 = qpos + GW_ACTIVE + lane;
         i0 = min(i0, i0 - ring_codes); /* unsigned: wraps when i0 >= ring_codes */
         i1 = min(i1, i1 - ring_codes);
@@ -222,48 +317,14 @@ struct PairQueue {
             queue[i0] = (CodeT)c0;
             queue[i1] = (CodeT)c1;
         }
-        qpos += 2 * GW_STEPS; /* this half's next group is two groups on */
+        qpos += GW_STEPS;
         qpos = min(qpos, qpos - ring_codes);
     }
+    __device__ __forceinline__ void end_pass(uint64_t pass) {
+        __syncwarp();
+        nb_arrive(bar + (int)(pass & 1));
+    }
 };
-
-template <int HALF, int PH, typename CodeT>
-__device__ __forceinline__ void pair_phase(uint32_t *ring, int l4, int lane, bool active, const FoldConst &mrow,
-                                           const FoldConst &mcol, uint32_t cols, PairQueue<CodeT> &q, int pair_bar) {
-    constexpr bool MINE = (PH & 1) == HALF;
-    uint4 x0 = make_uint4(0, 0, 0, 0), x1 = x0;
-    if (MINE) { /* part (1): the recurrence for this group */
-        GwOps o;
-        gw_load<PH>(ring, l4, o);
-        x0 = gw_twist4(o.a0, o.a04, o.c0, o.c04);
-        x1 = gw_twist4(o.a1, o.a14, o.c1, o.c14);
-        gw_store<PH>(ring, l4, active, x0, x1);
-    }
-    bar_sync(pair_bar, 64); /* the group is in the ring: the partner may start the next one */
-    if (MINE) {             /* part (2), beside the partner's part (1) */
-        const uint32_t c0 = gw_code(x0, mrow, mcol, cols);
-        const uint32_t c1 = gw_code(x1, mrow, mcol, cols);
-        q.put(c0, c1, lane, active);
-    }
-}
-
-template <int HALF, typename CodeT>
-__device__ __forceinline__ void pair_generate(uint32_t *ring, CodeT *queue, uint32_t ring_codes, uint32_t groups, int lane,
-                                              const FoldConst &mrow, const FoldConst &mcol, uint32_t cols, int pair_bar,
-                                              int pass_bar) {
-    const bool active = lane < GW_ACTIVE;
-    const int l4 = 4 * (active ? lane : GW_ACTIVE - 1); /* lanes 28..31 shadow lane 27, stores predicated off */
-    PairQueue<CodeT> q{queue, ring_codes, (uint32_t)(GW_STEPS * HALF)};
-    for (uint32_t g = 0; g < groups; g += 4) {
-        const uint32_t rest = groups - g; /* >= 1; the same in both halves */
-        pair_phase<HALF, 0>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
-        if (rest > 1) pair_phase<HALF, 1>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
-        if (rest > 2) pair_phase<HALF, 2>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
-        if (rest > 3) pair_phase<HALF, 3>(ring, l4, lane, active, mrow, mcol, cols, q, pair_bar);
-        bar_sync(pass_bar, 96); /* the pass is in the queue (both halves) and the consumer is done with the pass
-                                   before the previous one */
-    }
-}
 
 /* Per-lane counters of a consumer warp: payoffs are 0, 1, 2, so the three outcome counts come from two sums. */
 struct RolloutAcc {
@@ -320,7 +381,9 @@ struct TabAccess<false> {
     static __device__ __forceinline__ uint32_t u8(Addr a) { return __ldg(a); }
 };
 
-template <int KIND, typename CodeT, int Q, bool TAB_SMEM>
+/* DIR = 1: a backward stream — the batch's rollouts come in DESCENDING index order from i0 (rollout r of the batch is
+ * i0 - r) and a rollout's codes are stored last step first. */
+template <int KIND, typename CodeT, int Q, bool TAB_SMEM, int DIR>
 __device__ __forceinline__ void consume_batch(const Stream2Params &P, const CodeT *q, const uint8_t *tab, uint64_t i0,
                                               uint32_t live, int lane, RolloutAcc &acc) {
     using TA = TabAccess<TAB_SMEM>;
@@ -328,7 +391,10 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
     const uint32_t rl = (uint32_t)Q * lane;
     if (rl >= live) return;
     const uint32_t mine = (live - rl < (uint32_t)Q) ? live - rl : (uint32_t)Q; /* 1..Q rollouts of this lane */
-    const uint64_t il = i0 + rl;
+    const int cstep = DIR ? -1 : 1;                         /* direction of a rollout's codes in the queue */
+    const uint32_t cfirst = DIR ? d - 1 : 0;                /* queue offset of its first step */
+    auto index_of = [&](uint32_t j) -> uint64_t { return DIR ? i0 - (rl + j) : i0 + rl + j; };
+    const uint64_t il = DIR ? i0 - (rl + mine - 1) : i0 + rl; /* lowest rollout index of this lane */
     const int8_t *tb = reinterpret_cast<const int8_t *>(tab);
     const uint8_t *tch = tab + P.tab_len;
     uint32_t h[Q], pay[Q];
@@ -338,12 +404,12 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
             h[j] = PCU_HASH_INIT;
             pay[j] = 0;
             if ((uint32_t)j >= mine) continue;
-            const uint64_t i = il + j;
-            const CodeT *qc = q + (rl + j) * d;
+            const uint64_t i = index_of(j);
+            const CodeT *qc = q + (rl + j) * d + cfirst;
             uint8_t *tr = P.traj + (size_t)i * P.traj_stride * 3;
             if (KIND == KIND_MOLD) {
                 for (uint32_t s = 0; s < d; ++s) {
-                    const uint32_t code = qc[s];
+                    const uint32_t code = qc[cstep * (int)s];
                     h[j] = hash_step(h[j], code, 0);
                     put_traj<true>(tr, s, code, P.cols, 0, P.traj_stride);
                 }
@@ -351,7 +417,7 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
                 uint32_t g = (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base - P.gen_words;
                 int bias = P.bias ? P.bias[i] : P.bias_u;
                 for (uint32_t s = 0; s < d; ++s) {
-                    const uint32_t code = qc[s];
+                    const uint32_t code = qc[cstep * (int)s];
                     const uint32_t st = code * T;
                     const uint32_t ch = T > 1 ? (uint32_t)tch[g + 2 * st] : 0u;
                     const uint32_t t = g + P.gen_words + st + ch; /* discard(get_transition_idx): :88-89,149-152 */
@@ -373,17 +439,18 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
             const uint32_t jj = ((uint32_t)j < mine) ? (uint32_t)j : mine - 1;
             h[j] = PCU_HASH_INIT;
             pay[j] = 0;
-            qc[j] = q + (rl + jj) * d;
+            qc[j] = q + (rl + jj) * d + cfirst;
             if (KIND == KIND_TREE) {
-                p[j] = TA::at(tab, (P.state_pos ? P.state_pos[il + jj] : P.state_pos_u) - P.tab_base);
-                bias[j] = P.bias ? P.bias[il + jj] : P.bias_u;
+                const uint64_t i = index_of(jj);
+                p[j] = TA::at(tab, (P.state_pos ? P.state_pos[i] : P.state_pos_u) - P.tab_base);
+                bias[j] = P.bias ? P.bias[i] : P.bias_u;
             }
         }
         if (KIND == KIND_MOLD) {
 #pragma unroll 2
             for (uint32_t s = 0; s < d; ++s) {
 #pragma unroll
-                for (int j = 0; j < Q; ++j) h[j] = hash_step(h[j], qc[j][s], 0);
+                for (int j = 0; j < Q; ++j) h[j] = hash_step(h[j], qc[j][cstep * (int)s], 0);
             }
         } else if (T == 1) {
             const uint32_t adv = 2 + P.gen_words;
@@ -391,7 +458,7 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
             for (uint32_t s = 0; s < d; ++s) {
 #pragma unroll
                 for (int j = 0; j < Q; ++j) {
-                    const uint32_t code = qc[j][s];
+                    const uint32_t code = qc[j][cstep * (int)s];
                     const typename TA::Addr t = p[j] + code;
                     bias[j] += TA::s8(t);
                     p[j] = t + adv;
@@ -406,7 +473,7 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
             for (uint32_t s = 0; s < d; ++s) {
 #pragma unroll
                 for (int j = 0; j < Q; ++j) {
-                    const uint32_t code = qc[j][s];
+                    const uint32_t code = qc[j][cstep * (int)s];
                     const uint32_t st = code * T;
                     const uint32_t ch = TA::u8(p[j] + (tl + 2 * st)); /* the chance table follows the bias table */
                     const typename TA::Addr t = p[j] + (gen + st + ch);
@@ -426,8 +493,9 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
 #pragma unroll
     for (int j = 0; j < Q; ++j) {
         if ((uint32_t)j < mine) {
-            bytes |= pay[j] << (8 * j);
-            packed |= pay[j] << (2 * j);
+            const int slot = DIR ? (int)mine - 1 - j : j; /* position of rollout j in the lane's ascending vector */
+            bytes |= pay[j] << (8 * slot);
+            packed |= pay[j] << (2 * slot);
             acc.pay_sum += pay[j];
             acc.draws += pay[j] & 1u;
             acc.h += h[j];
@@ -442,82 +510,126 @@ __device__ __forceinline__ void consume_batch(const Stream2Params &P, const Code
         } else {
 #pragma unroll
             for (int j = 0; j < Q; ++j)
-                if ((uint32_t)j < mine) P.payoff[il + j] = (uint8_t)pay[j];
+                if ((uint32_t)j < mine) P.payoff[index_of(j)] = (uint8_t)pay[j];
         }
     }
-    if (Q == 4 && P.payoff_packed2) P.payoff_packed2[il >> 2] = (uint8_t)packed; /* il is a multiple of 4 (host-checked) */
+    /* packed: a forward lane's il is a multiple of 4 (host-checked); a backward stream only has whole batches, so its
+     * lanes hold four rollouts and il is a multiple of 4 as well */
+    if (Q == 4 && P.payoff_packed2) P.payoff_packed2[il >> 2] = (uint8_t)packed;
     if (P.traj_hash) {
         if (Q == 4 && P.vec_ok && mine == 4) {
-            *reinterpret_cast<uint4 *>(P.traj_hash + il) = make_uint4(h[0], h[1], h[2], h[3]);
+            *reinterpret_cast<uint4 *>(P.traj_hash + il) =
+                DIR ? make_uint4(h[3], h[2], h[1], h[0]) : make_uint4(h[0], h[1], h[2], h[3]);
         } else {
 #pragma unroll
             for (int j = 0; j < Q; ++j)
-                if ((uint32_t)j < mine) P.traj_hash[il + j] = h[j];
+                if ((uint32_t)j < mine) P.traj_hash[index_of(j)] = h[j];
         }
     }
 }
 
-/* The consumer warp of one stream: meets the generator halves at the pass barrier and plays every batch the pass
- * completed.  All stream-local arithmetic is 32-bit (a stream is < 2^32 steps: host-checked). */
-template <int KIND, typename CodeT, int Q, bool TAB_SMEM>
-__device__ __forceinline__ void consume_stream(const Stream2Params &P, const CodeT *queue, const uint8_t *tab, int pass_bar,
-                                               uint64_t first, uint32_t cnt, int lane, RolloutAcc &acc) {
+/* The consumer warp of one stream: waits for each pass of its generator and plays every batch the pass completed.
+ * All stream-local arithmetic is 32-bit (a stream is < 2^32 steps: host-checked).  `pro`: codes already in the queue
+ * before pass 0 (a backward stream's window steps). */
+template <int KIND, typename CodeT, int Q, bool TAB_SMEM, int DIR>
+__device__ __forceinline__ void consume_stream(const Stream2Params &P, const CodeT *queue, const uint8_t *tab, int bar,
+                                               uint64_t first, uint32_t cnt, uint32_t pro, uint32_t npass, int lane,
+                                               RolloutAcc &acc) {
     constexpr uint32_t RB = 32u * Q;
     const uint32_t d = P.depth;
     const uint32_t total_steps = cnt * d;
-    const uint32_t npass = (total_steps + GW_PASS_STEPS - 1) / GW_PASS_STEPS;
-    uint32_t r0 = 0;    /* first rollout of the next batch */
-    uint32_t qoff = 0;  /* its first code in the queue: (r0 * d) mod ring_codes, always a batch boundary */
-    uint32_t avail = 0; /* steps generated so far */
+    uint32_t r0 = 0;      /* first rollout (in generation order) of the next batch */
+    uint32_t qoff = 0;    /* its first code in the queue: always a batch boundary */
+    uint32_t avail = pro; /* steps generated so far */
     for (uint32_t j = 0; j < npass; ++j) {
-        bar_sync(pass_bar, 96);
+        nb_sync(bar + (int)(j & 1));
         avail = (total_steps - avail > (uint32_t)GW_PASS_STEPS) ? avail + GW_PASS_STEPS : total_steps;
         while (r0 < cnt) { /* every batch whose codes pass j completed */
             const uint32_t live = (cnt - r0 < RB) ? cnt - r0 : RB;
             if ((r0 + live) * d > avail) break;
-            consume_batch<KIND, CodeT, Q, TAB_SMEM>(P, queue + qoff, tab, first + r0, live, lane, acc);
+            consume_batch<KIND, CodeT, Q, TAB_SMEM, DIR>(P, queue + qoff, tab, DIR ? first + (cnt - 1 - r0) : first + r0, live,
+                                                         lane, acc);
             r0 += RB;
             qoff += P.bcodes;
             if (qoff >= P.ring_codes) qoff = 0;
         }
+        if (j + 2 < npass) {
+            __syncwarp();
+            nb_arrive(bar + 2 + (int)(j & 1));
+        }
     }
 }
 
+template <int KIND, typename CodeT, bool TAB_SMEM, int DIR>
+__device__ __forceinline__ void consume_any(const Stream2Params &P, const CodeT *queue, const uint8_t *tab, int bar,
+                                            uint64_t first, uint32_t cnt, uint32_t pro, uint32_t npass, int lane,
+                                            RolloutAcc &acc) {
+    if (P.rb == 128)
+        consume_stream<KIND, CodeT, 4, TAB_SMEM, DIR>(P, queue, tab, bar, first, cnt, pro, npass, lane, acc);
+    else if (P.rb == 64)
+        consume_stream<KIND, CodeT, 2, TAB_SMEM, DIR>(P, queue, tab, bar, first, cnt, pro, npass, lane, acc);
+    else
+        consume_stream<KIND, CodeT, 1, TAB_SMEM, DIR>(P, queue, tab, bar, first, cnt, pro, npass, lane, acc);
+}
+
 template <int KIND, typename CodeT, bool TAB_SMEM>
-__global__ void __launch_bounds__(SP_THREADS) k_stream2(const Stream2Params P) {
+__global__ void __launch_bounds__(GW_PAIRS * 64, 2) k_stream2(const Stream2Params P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t d = P.depth;
-    /* layout: rings [SP_STREAMS][896] u32 | queues [SP_STREAMS][ring_codes + 16] CodeT | tables */
+    /* layout: rings [PAIRS][896] u32 | queues [PAIRS][ring_codes + 16] CodeT | tables */
     uint32_t *rings = reinterpret_cast<uint32_t *>(smem_raw);
-    CodeT *queues = reinterpret_cast<CodeT *>(rings + SP_STREAMS * GW_RING);
+    CodeT *queues = reinterpret_cast<CodeT *>(rings + GW_PAIRS * GW_RING);
     const uint32_t R = P.ring_codes;
     const uint8_t *tab = P.tab;
     if (KIND == KIND_TREE && TAB_SMEM) {
-        uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)SP_STREAMS * (R + 16));
+        uint8_t *stab = reinterpret_cast<uint8_t *>(queues + (size_t)GW_PAIRS * (R + 16));
         stab = reinterpret_cast<uint8_t *>(((uintptr_t)stab + 15) & ~(uintptr_t)15);
         const uint32_t bytes = P.tab_len * (P.T > 1 ? 2u : 1u);
         for (uint32_t i = tid; i < bytes; i += blockDim.x) stab[i] = P.tab[i];
         tab = stab;
     }
-    const int sl = warp % SP_STREAMS;   /* stream of this warp within the CTA: its three warps share a sub-partition */
-    const int role = warp / SP_STREAMS; /* 0, 1: generator halves A, B; 2: consumer */
-    const uint32_t stream = blockIdx.x * SP_STREAMS + sl;
-    uint32_t *ring = rings + sl * GW_RING;
-    CodeT *queue = queues + (size_t)sl * (R + 16);
-    const int pair_bar = 1 + sl, pass_bar = 1 + SP_STREAMS + sl; /* barrier 0 is __syncthreads, used once below */
-    if (stream < P.streams && role == 0) gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
+    const int pair = warp % GW_PAIRS;
+    const bool is_gen = warp < GW_PAIRS;
+    const uint32_t stream = blockIdx.x * GW_PAIRS + pair;
+    uint32_t *ring = rings + pair * GW_RING;
+    CodeT *queue = queues + (size_t)pair * (R + 16);
+    /* four named barriers per pair; id 0 doubles as __syncthreads, used only below, before any pair starts */
+    const int bar = 4 * pair;
+    /* stream sigma: even -> forwards from window sigma / 2; odd -> backwards from window (sigma + 1) / 2, except the
+     * batch's last stream, which runs forwards from the extra window behind the regular ones */
+    const bool last = stream + 1 == P.streams;
+    const bool backward = (stream & 1u) && !last;
+    const uint32_t ck = (stream & 1u) ? (last ? P.ck_regular : (stream + 1) / 2) : stream / 2;
+    if (stream < P.streams && is_gen) {
+        if (backward)
+            gw_load_window_b(ring, P.checkpoints + (size_t)ck * MT_N, lane);
+        else
+            gw_load_window(ring, P.checkpoints + (size_t)ck * MT_N, lane);
+    }
     __syncthreads();
     if (stream >= P.streams) return;
 
     const uint64_t first = (uint64_t)stream * P.chunk;
     const uint32_t cnt = (uint32_t)((first + P.chunk <= P.n) ? P.chunk : P.n - first);
     const uint32_t total_steps = cnt * d;
-    const uint32_t groups = (total_steps + GW_STEPS - 1) / GW_STEPS;
+    /* a backward stream's first 156 steps are the window itself */
+    const uint32_t pro = backward ? (total_steps < (uint32_t)GW_WINDOW_STEPS ? total_steps : (uint32_t)GW_WINDOW_STEPS) : 0u;
+    const uint32_t groups = (total_steps - pro + GW_STEPS - 1) / GW_STEPS;
+    const uint32_t npass = groups ? (groups + 3) / 4 : 1u; /* a stream without a generated group still hands over once */
 
-    if (role == 0) {
-        pair_generate<0, CodeT>(ring, queue, R, groups, lane, P.mrow, P.mcol, P.cols, pair_bar, pass_bar);
-        if (stream + 1 == P.streams && P.end_window) {
+    if (is_gen) {
+        QueueSink<CodeT> sink{queue, R, bar, lane, pro};
+        if (backward) {
+            for (uint32_t t = lane; t < pro; t += 32) /* codes of the window's own steps: temper + reduce only */
+                queue[t] = (CodeT)gw_code_b(*reinterpret_cast<const uint4 *>(ring + 48 + 4 * t), P.mrow, P.mcol, P.cols);
+            __syncwarp();
+            gw_generate<1>(ring, groups, lane, P.mrow, P.mcol, P.cols, sink);
+        } else {
+            gw_generate<0>(ring, groups, lane, P.mrow, P.mcol, P.cols, sink);
+        }
+        if (groups == 0) sink.end_pass(0);
+        if (last && P.end_window) {
             /* words generated in the current pass before the stream's end: 4 * total_steps mod 896,
              * except that a stream ending exactly on a pass boundary sits at 896 */
             const uint64_t words = 4ull * total_steps;
@@ -527,19 +639,13 @@ __global__ void __launch_bounds__(SP_THREADS) k_stream2(const Stream2Params P) {
         }
         return;
     }
-    if (role == 1) {
-        pair_generate<1, CodeT>(ring, queue, R, groups, lane, P.mrow, P.mcol, P.cols, pair_bar, pass_bar);
-        return;
-    }
 
     /* ---- consumer warp */
     RolloutAcc acc;
-    if (P.rb == 128)
-        consume_stream<KIND, CodeT, 4, TAB_SMEM>(P, queue, tab, pass_bar, first, cnt, lane, acc);
-    else if (P.rb == 64)
-        consume_stream<KIND, CodeT, 2, TAB_SMEM>(P, queue, tab, pass_bar, first, cnt, lane, acc);
+    if (backward)
+        consume_any<KIND, CodeT, TAB_SMEM, 1>(P, queue, tab, bar, first, cnt, pro, npass, lane, acc);
     else
-        consume_stream<KIND, CodeT, 1, TAB_SMEM>(P, queue, tab, pass_bar, first, cnt, lane, acc);
+        consume_any<KIND, CodeT, TAB_SMEM, 0>(P, queue, tab, bar, first, cnt, pro, npass, lane, acc);
     if (P.sums) {
         unsigned long long pay_sum = warp_sum_u64(acc.pay_sum), draws = warp_sum_u64(acc.draws), n = warp_sum_u64(acc.n);
         const unsigned long long h = warp_sum_u64(acc.h);
@@ -599,7 +705,7 @@ __global__ void __launch_bounds__(128) k_gen_codes2(const Gen2Params P) {
     gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
     __syncwarp();
     GlobalSink<CodeT> sink{reinterpret_cast<CodeT *>(P.codes) + first, last - first, lane};
-    gw_generate(ring, (last - first + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
+    gw_generate<0>(ring, (last - first + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
     if (stream + 1 == P.streams && P.end_window) {
         const uint64_t words = 4 * (last - first);
         uint32_t w_end = (uint32_t)(words % GW_RING);

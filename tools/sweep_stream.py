@@ -14,7 +14,7 @@ def main():
     ctx.set_stream(torch.cuda.current_stream().cuda_stream)
     cfgs = {"A": dict(rows=3, cols=3, transitions=1, depth=10), "B": dict(rows=9, cols=9, transitions=3, depth=20)}
     for name in sys.argv[1:] or ["A"]:
-        for sps in (2, 4, 6, 8):
+        for sps in (4, 8, 16):
             ctx.set_option("streams_per_sm", sps)
             ks, ts = [], []
             for it in range(6):
