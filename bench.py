@@ -608,12 +608,20 @@ def run_ours(args, w, workload_name):
 
     single = None
     if world > 1 and not args.no_extra:
+        # the other ranks must leave their GPUs IDLE meanwhile: they wait on the rendezvous store (a host-side wait),
+        # not in an NCCL barrier, whose kernel would spin on the very GPUs rank 0's context is about to use
+        from torch.distributed.distributed_c10d import _get_default_store
+
         rig.barrier()
+        store = _get_default_store()
         if rank == 0:
             try:
                 single = single_process_line(args, w, world, depth)
             except Exception as exc:
                 single = {"error": str(exc)[:300]}
+            store.set("pinyon_single_process_done", "1")
+        else:
+            store.wait(["pinyon_single_process_done"])
         rig.barrier()
 
     if rank == 0:

@@ -201,6 +201,7 @@ struct Multi {
     uint64_t *pin_sums = nullptr;
     uint64_t min_rollouts = 0; /* batches below this many rollouts go to the first GPU alone */
     uint64_t nccl_calls = 0;
+    double t_dispatch_ms = 0, t_reduce_ms = 0, t_sync_ms = 0; /* host wall clock of the last call's phases */
 };
 
 namespace {
@@ -1867,6 +1868,10 @@ int multi_dispatch(pcu_ctx *ctx, const std::vector<ShardPlan> &plan, uint64_t ch
     Multi &M = *ctx->multi;
     const size_t G = M.kids.size();
     std::vector<int> rcs(G, PCU_OK);
+    const auto t_begin = std::chrono::steady_clock::now();
+    auto ms_since = [](std::chrono::steady_clock::time_point t) {
+        return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t).count();
+    };
     for (size_t g = 0; g < G; ++g) {
         pcu_ctx *kid = M.kids[g];
         kid->hint = pcu_ctx::ShardHint{};
@@ -1887,6 +1892,8 @@ int multi_dispatch(pcu_ctx *ctx, const std::vector<ShardPlan> &plan, uint64_t ch
             rc = rcs[g];
             ctx->err = "GPU " + std::to_string(M.kids[g]->device) + ": " + M.kids[g]->err;
         }
+    M.t_dispatch_ms = ms_since(t_begin);
+    const auto t_reduce = std::chrono::steady_clock::now();
     /* ---- the collective: counters of every shard summed on every GPU */
     std::vector<size_t> act;
     for (size_t g = 0; g < G; ++g)
@@ -1930,6 +1937,8 @@ int multi_dispatch(pcu_ctx *ctx, const std::vector<ShardPlan> &plan, uint64_t ch
                 rc = fail(ctx, PCU_ERR_CUDA, "copying the reduced counters failed");
         }
     }
+    M.t_reduce_ms = ms_since(t_reduce);
+    const auto t_sync = std::chrono::steady_clock::now();
     /* ---- every shard's outputs are complete once its stream drains */
     for (size_t g = 0; g < G; ++g) {
         pcu_ctx *kid = M.kids[g];
@@ -1937,6 +1946,7 @@ int multi_dispatch(pcu_ctx *ctx, const std::vector<ShardPlan> &plan, uint64_t ch
         const cudaError_t e = cudaStreamSynchronize(kid->stream);
         if (e != cudaSuccess && !rc) rc = fail(ctx, PCU_ERR_CUDA, "GPU %d: %s", kid->device, cudaGetErrorString(e));
     }
+    M.t_sync_ms = ms_since(t_sync);
     if (!rc) {
         if (out->sums) {
             if (act.empty())
@@ -2143,6 +2153,9 @@ int pcu_get_stat(pcu_ctx *ctx, const char *key, double *value) {
         else *value = c->last_family_ms;
     } else if (!strcmp(key, "last_table_build_ms")) *value = c->last_table_ms;
     else if (!strcmp(key, "nccl_calls")) *value = ctx->multi ? (double)ctx->multi->nccl_calls : 0.0;
+    else if (!strcmp(key, "multi_dispatch_ms")) *value = ctx->multi ? ctx->multi->t_dispatch_ms : 0.0;
+    else if (!strcmp(key, "multi_reduce_ms")) *value = ctx->multi ? ctx->multi->t_reduce_ms : 0.0;
+    else if (!strcmp(key, "multi_sync_ms")) *value = ctx->multi ? ctx->multi->t_sync_ms : 0.0;
     else return fail(ctx, PCU_ERR_INVALID, "unknown statistic %s", key);
     return PCU_OK;
 }

@@ -212,9 +212,13 @@ __device__ __forceinline__ void gw_generate(uint32_t *ring, uint64_t groups, int
 #define GW_BODY(PH, NEXT)                                                                                  \
     {                                                                                                      \
         if (NEXT) GW_LOAD(((PH) + 1) & 3)                                                                  \
-        const uint32_t c0 = DIR == 0 ? gw_code(x0, mrow, mcol, cols) : gw_code_b(x0, mrow, mcol, cols);    \
-        const uint32_t c1 = DIR == 0 ? gw_code(x1, mrow, mcol, cols) : gw_code_b(x1, mrow, mcol, cols);    \
-        sink.put(g + (PH), c0, c1, active);                                                                \
+        if constexpr (Sink::WORDS) {                                                                       \
+            sink.put_words(g + (PH), x0, x1, active);                                                      \
+        } else {                                                                                           \
+            const uint32_t c0 = DIR == 0 ? gw_code(x0, mrow, mcol, cols) : gw_code_b(x0, mrow, mcol, cols); \
+            const uint32_t c1 = DIR == 0 ? gw_code(x1, mrow, mcol, cols) : gw_code_b(x1, mrow, mcol, cols); \
+            sink.put(g + (PH), c0, c1, active);                                                            \
+        }                                                                                                  \
         if (NEXT) {                                                                                        \
             GW_TWIST()                                                                                     \
             gw_store<((PH) + 1) & 3>(ring, l4, active, x0, x1);                                            \
@@ -300,6 +304,7 @@ __device__ __forceinline__ void nb_arrive(int id) {
  * 156 codes a backward stream takes from its window before pass 0). */
 template <typename CodeT>
 struct QueueSink {
+    static constexpr bool WORDS = false;
     CodeT *queue;
     uint32_t ring_codes;
     int bar;
@@ -681,6 +686,7 @@ struct Gen2Params {
 
 template <typename CodeT>
 struct GlobalSink {
+    static constexpr bool WORDS = false;
     CodeT *codes; /* first code of this stream */
     uint64_t count;
     int lane;
@@ -705,6 +711,45 @@ __global__ void __launch_bounds__(128) k_gen_codes2(const Gen2Params P) {
     gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
     __syncwarp();
     GlobalSink<CodeT> sink{reinterpret_cast<CodeT *>(P.codes) + first, last - first, lane};
+    gw_generate<0>(ring, (last - first + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
+    if (stream + 1 == P.streams && P.end_window) {
+        const uint64_t words = 4 * (last - first);
+        uint32_t w_end = (uint32_t)(words % GW_RING);
+        if (w_end == 0 && words > 0) w_end = GW_RING;
+        gw_dump_window(ring, w_end, P.end_window, lane);
+    }
+}
+
+/* ------------------------------------------------------------------ k_gen_words */
+/* The model stream itself — four tempered words per step — to global memory, for the variant kernel (thread.cuh),
+ * whose action counts change from step to step and cannot be folded into the generator. */
+struct WordSink {
+    static constexpr bool WORDS = true;
+    uint4 *words; /* first step of this stream */
+    uint64_t count;
+    int lane;
+    __device__ __forceinline__ void begin_pass(uint64_t) {}
+    __device__ __forceinline__ void put_words(uint64_t g, const uint4 &x0, const uint4 &x1, bool active) {
+        const uint64_t q = g * GW_STEPS + lane;
+        if (active && q < count) words[q] = make_uint4(mt_temper(x0.x), mt_temper(x0.y), mt_temper(x0.z), mt_temper(x0.w));
+        if (active && q + GW_ACTIVE < count)
+            words[q + GW_ACTIVE] = make_uint4(mt_temper(x1.x), mt_temper(x1.y), mt_temper(x1.z), mt_temper(x1.w));
+    }
+    __device__ __forceinline__ void put(uint64_t, uint32_t, uint32_t, bool) {}
+    __device__ __forceinline__ void end_pass(uint64_t) {}
+};
+
+static __global__ void __launch_bounds__(128) k_gen_words(const Gen2Params P) {
+    __shared__ __align__(16) uint32_t rings[4 * GW_RING];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t stream = blockIdx.x * 4 + warp;
+    if (stream >= P.streams) return;
+    uint32_t *ring = rings + warp * GW_RING;
+    const uint64_t first = (uint64_t)stream * P.chunk_steps;
+    const uint64_t last = (first + P.chunk_steps < P.total_steps) ? first + P.chunk_steps : P.total_steps;
+    gw_load_window(ring, P.checkpoints + (size_t)stream * MT_N, lane);
+    __syncwarp();
+    WordSink sink{reinterpret_cast<uint4 *>(P.codes) + first, last - first, lane};
     gw_generate<0>(ring, (last - first + GW_STEPS - 1) / GW_STEPS, lane, P.mrow, P.mcol, P.cols, sink);
     if (stream + 1 == P.streams && P.end_window) {
         const uint64_t words = 4 * (last - first);
