@@ -116,12 +116,22 @@ void pcu_host_free(pcu_ctx *ctx, void *p);
 #define PCU_MODEL_PER_ROLLOUT 1
 #define PCU_MODEL_WORDS 2
 
+/* Which PRNG type the type list uses (Types::PRNG, src/types/types.hh:27-76) — for the model AND the states of the
+ * batch.  PCU_ENGINE_XOR_SHIFT is Pinyon's xor_shift (random.hh:66-121; it needs a random_seed() member added to
+ * satisfy IsPRNG): 64 bits of state, one step per draw.  With it, mode S takes the model engine's
+ * state in *xs_state (updated in place), mode P takes states in seeds[], mode W is not offered, and a RandomTree
+ * batch carries in state_seed the state engine's CURRENT 64-bit state (state_pos is ignored). */
+#define PCU_ENGINE_MT19937 0
+#define PCU_ENGINE_XOR_SHIFT 1
+
 typedef struct {
     int32_t mode;
     uint32_t *mt_x;        /* mode S: [624] engine words, HOST memory, updated in place */
     uint32_t *mt_p;        /* mode S: next-word position 0..624, HOST memory, updated in place */
     const uint64_t *seeds; /* mode P: [n] seeds, in the memory space of the batch */
     const uint32_t *words; /* mode W: [4 * sum of depths] raw engine words, in the memory space of the batch */
+    uint32_t engine;       /* PCU_ENGINE_* */
+    uint64_t *xs_state;    /* xor_shift, mode S: the model engine's state, HOST memory, updated in place */
 } pcu_model_rng;
 
 /* Host-side engine helpers (no GPU needed).  pcu_mt_seed == std::mt19937::seed as
@@ -133,6 +143,8 @@ uint32_t pcu_mt_next(uint32_t *mt_x, uint32_t *mt_p);
 /* The next n RAW (untempered) state words of the engine, which is advanced by n draws: the words a mode-W rollout of
  * n / 4 steps consumes.  pcu_mt_next(...) == temper(raw word). */
 int pcu_mt_take_raw(uint32_t *mt_x, uint32_t *mt_p, uint64_t n, uint32_t *out);
+/* xor_shift::discard (random.hh:107-111) in O(64^2 log n): the state after n steps. */
+uint64_t pcu_xs_discard(uint64_t state, uint64_t n);
 /* Diagnostic: the engine advanced by c * stride draws through the cached polynomial family
  * x^(c * stride) mod phi that the device jump-ahead uses for its checkpoints (c < 65536). */
 int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint64_t c);
@@ -153,7 +165,14 @@ int pcu_mt_discard_family(uint32_t *mt_x, uint32_t *mt_p, uint64_t stride, uint6
  *                    reference never terminates from a depth_bound == 0 root (:95-99)
  *   payoff_bias      (:20)
  *   rows, cols, transitions, chance_threshold = thr_p/thr_q  (:17-21) batch-uniform
- * Only the default growth functions (:141-146) are reproduced. */
+ *   growth           which growth functions the states carry (:25-27): PCU_GROWTH_DEFAULT (:141-146), or
+ *                    PCU_GROWTH_ALTERNATING_CONSTANT = GrowLib::alternating_constant_actions (libpinyon/grow-lib.hh:16-24)
+ *                    as actions_func with the default depth and bias functions — rows and cols then change from step to
+ *                    step.  (grow-lib's other function calls a prng member that does not exist and cannot be instantiated.)
+ * Other growth functions are host function pointers and are refused by the drop-in model. */
+#define PCU_GROWTH_DEFAULT 0
+#define PCU_GROWTH_ALTERNATING_CONSTANT 1
+
 typedef struct {
     uint64_t n;
     int32_t mem;
@@ -169,6 +188,7 @@ typedef struct {
     int32_t payoff_bias_u;
     uint32_t rows, cols, transitions;
     int32_t thr_p, thr_q;
+    uint32_t growth;
 } pcu_rt_batch;
 
 /* MoldState batch (test-states.hh:13-24): n_actions uniform, max_depth per rollout. */

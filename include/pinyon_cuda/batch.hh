@@ -11,6 +11,8 @@
 #include <type_traits>
 #include <vector>
 
+#include <libpinyon/grow-lib.hh>
+
 #include "device.hh"
 
 namespace PinyonCuda {
@@ -37,6 +39,7 @@ concept IsMoldState = requires(S &s) { s.max_depth; } && !IsRandomTreeState<S>;
 struct Shape {
     uint32_t rows = 0, cols = 0, transitions = 1;
     int32_t thr_p = 0, thr_q = 1;
+    uint32_t growth = 0; /* PCU_GROWTH_* */
     bool operator==(const Shape &) const = default;
 };
 
@@ -102,9 +105,14 @@ struct TreeImage {
 template <IsRandomTreeState State>
 TreeImage serialise_tree(const State &s, StreamLocator &locator) {
     using PRNG = std::remove_cvref_t<decltype(s.device)>;
-    if (s.depth_bound_func != &State::depth_bound_default || s.actions_func != &State::actions_default ||
-        s.payoff_bias_func != &State::payoff_bias_default)
-        throw Error(PCU_ERR_UNSUPPORTED, "RandomTree growth functions other than the defaults are host code");
+    uint32_t growth = PCU_GROWTH_DEFAULT;
+    if (s.actions_func == &GrowLib::alternating_constant_actions<State>)
+        growth = PCU_GROWTH_ALTERNATING_CONSTANT; /* the one instantiable grow-lib function (libpinyon/grow-lib.hh:16-24) */
+    else if (s.actions_func != &State::actions_default)
+        throw Error(PCU_ERR_UNSUPPORTED, "RandomTree actions_func other than the default / GrowLib::alternating_constant_actions");
+    if (s.depth_bound_func != &State::depth_bound_default || s.payoff_bias_func != &State::payoff_bias_default)
+        throw Error(PCU_ERR_UNSUPPORTED, "RandomTree depth/bias growth functions other than the defaults are host code");
+
     if (s.chance_denominator != 10) throw Error(PCU_ERR_UNSUPPORTED, "chance_denominator != 10");
     if (s.depth_bound == 0 || s.depth_bound > 65535)
         throw Error(PCU_ERR_INVALID, "depth_bound must be 1..65535 (0 never terminates, random-tree.hh:95-99)");
@@ -119,16 +127,23 @@ TreeImage serialise_tree(const State &s, StreamLocator &locator) {
         t.shape.thr_p = -t.shape.thr_p;
     }
     if (t.shape.thr_p < 0) t.shape.thr_p = 0; /* x >= 1/10 > any negative threshold */
-    t.state_seed = EngineAccess<PRNG>::seed(s.device);
+    t.shape.growth = growth;
     t.transition_seed = static_cast<uint64_t>(s.transition_seed);
     t.depth = static_cast<uint16_t>(s.depth_bound);
     t.payoff_bias = s.payoff_bias;
-    EngineImage img;
-    EngineAccess<PRNG>::read(s.device, img);
-    const uint64_t pos = locator.locate(t.state_seed, img);
-    if (pos == UINT64_MAX || pos > 0xffffffffull)
-        throw Error(PCU_ERR_UNSUPPORTED, "state.device is not within 2^32 draws of prng{device.get_seed()}");
-    t.state_pos = static_cast<uint32_t>(pos);
+    if constexpr (EngineAccess<PRNG>::ENGINE == PCU_ENGINE_XOR_SHIFT) {
+        t.state_seed = EngineAccess<PRNG>::state(s.device); /* the whole engine: its current 64-bit state */
+        t.state_pos = 0;
+        (void)locator;
+    } else {
+        t.state_seed = EngineAccess<PRNG>::seed(s.device);
+        EngineImage img;
+        EngineAccess<PRNG>::read(s.device, img);
+        const uint64_t pos = locator.locate(t.state_seed, img);
+        if (pos == UINT64_MAX || pos > 0xffffffffull)
+            throw Error(PCU_ERR_UNSUPPORTED, "state.device is not within 2^32 draws of prng{device.get_seed()}");
+        t.state_pos = static_cast<uint32_t>(pos);
+    }
     return t;
 }
 

@@ -359,6 +359,7 @@ class LeafBatcher {
             tb.transitions = b.shape.transitions;
             tb.thr_p = b.shape.thr_p;
             tb.thr_q = b.shape.thr_q;
+            tb.growth = b.shape.growth;
             /* batch-uniform fields travel as scalars: leaves of searches from one root share the state seed and
              * take the library's state-stream table kernel */
             if (all_equal(b.state_seed)) tb.state_seed_u = b.state_seed[0]; else tb.state_seed = b.state_seed.data();
@@ -453,6 +454,7 @@ struct BatchedMonteCarloModel : MonteCarloModel<Types, has_policy> {
             /* the words this model's engine draws for the rollout: 2 random_int per step, 2 words each
              * (monte-carlo-model.hh:89-90; random.hh:26,28); `device` ends where the reference model's would */
             using Access = EngineAccess<typename Types::PRNG>;
+            static_assert(Access::ENGINE == PCU_ENGINE_MT19937, "the batching adapter (model-rng mode W) serves prng type lists");
             EngineImage img;
             Access::read(this->device, img);
             uint32_t small[4 * 64];

@@ -20,6 +20,7 @@
 #include <random>
 #include <sstream>
 #include <stdexcept>
+#include <type_traits>
 
 #include <types/random.hh>
 
@@ -107,15 +108,44 @@ inline void write_engine(std::mt19937 &e, const EngineImage &img) {
 
 }  // namespace detail
 
-/* Customisation point: how to get at the MT19937 of a Types::PRNG. */
+/* Pinyon's xor_shift (random.hh:66-121) lacks the random_seed() member IsPRNG demands (types.hh:165-190), so no type
+ * list can name it as shipped.  This is the class with that one member added — what a user has to write anyway:
+ *     using XsTypes = DefaultTypes<double, int, int, double, ConstantSum<1, 1>::Value, std::vector, Matrix, std::mutex,
+ *                                  uint64_t, PinyonCuda::xor_shift_prng>;                                          */
+struct xor_shift_prng : xor_shift {
+    using xor_shift::xor_shift;
+    uint64_t random_seed() { return uniform_64(); }
+};
+
+namespace detail {
+struct XsStateTag {
+    using type = uint64_t xor_shift::*;
+    friend type pinyon_cuda_get(XsStateTag);
+};
+template struct PrivateAccess<XsStateTag, &xor_shift::state>;
+inline uint64_t &xs_state_of(xor_shift &p) { return p.*pinyon_cuda_get(XsStateTag{}); }
+inline const uint64_t &xs_state_of(const xor_shift &p) { return p.*pinyon_cuda_get(XsStateTag{}); }
+}  // namespace detail
+
+/* Customisation point: how to get at the engine of a Types::PRNG.  ENGINE is the C ABI's PCU_ENGINE_* value. */
 template <typename PRNG>
 struct EngineAccess;
 
 template <>
 struct EngineAccess<prng> {
+    static constexpr uint32_t ENGINE = 0; /* PCU_ENGINE_MT19937 */
     static void read(const prng &device, EngineImage &img) { detail::read_engine(detail::engine_of(device), img); }
     static void write(prng &device, const EngineImage &img) { detail::write_engine(detail::engine_of(device), img); }
     static uint64_t seed(const prng &device) { return device.get_seed(); }
+};
+
+/* xor_shift and anything derived from it: the whole engine is one 64-bit word. */
+template <typename PRNG>
+    requires std::is_base_of_v<xor_shift, PRNG>
+struct EngineAccess<PRNG> {
+    static constexpr uint32_t ENGINE = 1; /* PCU_ENGINE_XOR_SHIFT */
+    static uint64_t state(const PRNG &device) { return detail::xs_state_of(device); }
+    static void set_state(PRNG &device, uint64_t s) { detail::xs_state_of(device) = s; }
 };
 
 }  // namespace PinyonCuda

@@ -96,6 +96,7 @@ struct MonteCarloModel : Types {
                 b.transitions = t.shape.transitions;
                 b.thr_p = t.shape.thr_p;
                 b.thr_q = t.shape.thr_q;
+                b.growth = t.shape.growth;
                 with_engine([&](pcu_model_rng &rng) { gpu->check(pcu_rollout_random_tree(gpu->ctx, &b, &rng, &out)); });
                 output.value = value_from_code(payoff);
             } else {
@@ -180,14 +181,22 @@ struct MonteCarloModel : Types {
         template <typename F>
         void with_engine(F &&call) {
             using Access = EngineAccess<typename Types::PRNG>;
-            EngineImage img;
-            Access::read(device, img);
             pcu_model_rng rng{};
             rng.mode = PCU_MODEL_STREAM;
-            rng.mt_x = img.x.data();
-            rng.mt_p = &img.p;
-            call(rng);
-            Access::write(device, img); /* `device` continues where the CPU model's would */
+            rng.engine = Access::ENGINE;
+            if constexpr (Access::ENGINE == PCU_ENGINE_XOR_SHIFT) {
+                uint64_t st = Access::state(device);
+                rng.xs_state = &st;
+                call(rng);
+                Access::set_state(device, st);
+            } else {
+                EngineImage img;
+                Access::read(device, img);
+                rng.mt_x = img.x.data();
+                rng.mt_p = &img.p;
+                call(rng);
+                Access::write(device, img); /* `device` continues where the CPU model's would */
+            }
         }
 
         static uint16_t checked_depth(size_t max_depth) {
@@ -244,6 +253,7 @@ struct MonteCarloModel : Types {
                 b.transitions = sh.transitions;
                 b.thr_p = sh.thr_p;
                 b.thr_q = sh.thr_q;
+                b.growth = sh.growth;
                 /* batch-uniform fields travel as scalars: a batch of leaves of one root then takes
                  * the library's shared-stream kernel */
                 if (all_equal(in.state_seed, first, last))

@@ -65,6 +65,9 @@ def load_oracle() -> C.CDLL:
     lib.orc_mt_state.argtypes = [u64, u64, vp, vp]
     lib.orc_set_model_engine.argtypes = [vp, u32]
     lib.orc_set_model_engine.restype = None
+    lib.orc_set_engine_kind.argtypes = [C.c_int]
+    lib.orc_set_growth.argtypes = [C.c_int]
+    lib.orc_set_state_after_ctor.argtypes = [vp]
     lib.orc_random_tree_root_strategies.argtypes = [u64, u64, u32, u32, u32, u32, C.c_int, C.c_int, vp]
     return lib
 
@@ -83,6 +86,12 @@ def load_reference():
             lib.ref_random_tree_rollouts.restype = u64
             lib.ref_mold_rollouts.argtypes = [u64, u32, vp, u32, vp, u64, u64, vp, vp, vp, u32]
             lib.ref_mold_rollouts.restype = u64
+            if hasattr(lib, "ref_xs_random_tree_rollouts"):  # variants: xor_shift type list, grow-lib growth function
+                lib.ref_xs_random_tree_rollouts.argtypes = _RT_ARGS + [vp]
+                lib.ref_xs_random_tree_rollouts.restype = u64
+                lib.ref_xs_mold_rollouts.argtypes = [u64, u32, vp, u32, vp, u64, u64, vp, vp, vp, u32]
+                lib.ref_xs_mold_rollouts.restype = u64
+                lib.ref_set_growth.argtypes = [C.c_int]
             for fn in ("ref_prng_uniform_64", "ref_prng_uniform"):
                 getattr(lib, fn).argtypes = [u64, u64, u64, vp]
             lib.ref_prng_random_int.argtypes = [u64, u64, C.c_int, u64, vp]
@@ -112,7 +121,7 @@ def _arr(a, dtype):
 
 def random_tree_rollouts(lib, n, *, rows, cols, transitions=1, thr=(0, 1), depth, state_seed=0, state_pre_discard=0,
                          transition_seed=0, payoff_bias=0, model_seed=0, model_pre_discard=0, model_seeds=None,
-                         want_traj=True, prefix="orc"):
+                         want_traj=True, prefix="orc", engine="mt", growth=0):
     """Run n RandomTree rollouts on a checker library.  `prefix` "orc" = restatement,
     "ref" = compiled reference.  Per-rollout numpy arrays or batch-uniform scalars.
     NOTE: states are described the reference's way — seed plus draws discarded BEFORE
@@ -130,19 +139,38 @@ def random_tree_rollouts(lib, n, *, rows, cols, transitions=1, thr=(0, 1), depth
     args = [n, p(ss), ss_u, p(sp), sp_u, p(ts), ts_u, p(dp), dp_u, p(pb), pb_u, rows, cols, transitions, thr[0], thr[1],
             p(ms), model_seed, model_pre_discard, p(payoff), p(traj), max(dmax, 1)]
     res = {"payoff": payoff, "traj": traj}
+    # engine="xs": Pinyon's xor_shift PRNG (seeds are then engine STATES); growth=1: GrowLib::alternating_constant_actions
+    state_after = np.zeros(n, np.uint64) if engine == "xs" else None
     if prefix == "orc":
         th = np.zeros(n, np.uint32)
         sums = np.zeros(8, np.uint64)
-        steps = lib.orc_random_tree_rollouts(*args, p(th), p(sums))
+        lib.orc_set_engine_kind(1 if engine == "xs" else 0)
+        lib.orc_set_growth(growth)
+        lib.orc_set_state_after_ctor(p(state_after))
+        try:
+            steps = lib.orc_random_tree_rollouts(*args, p(th), p(sums))
+        finally:
+            lib.orc_set_engine_kind(0)
+            lib.orc_set_growth(0)
+            lib.orc_set_state_after_ctor(None)
         res.update(traj_hash=th, sums=sums)
     else:
-        steps = lib.ref_random_tree_rollouts(*args)
+        lib.ref_set_growth(growth)
+        try:
+            if engine == "xs":
+                steps = lib.ref_xs_random_tree_rollouts(*args, p(state_after))
+            else:
+                steps = lib.ref_random_tree_rollouts(*args)
+        finally:
+            lib.ref_set_growth(0)
+    if state_after is not None:
+        res["state_after_ctor"] = state_after
     res["steps"] = steps
     return res
 
 
 def mold_rollouts(lib, n, *, n_actions, depth, model_seed=0, model_pre_discard=0, model_seeds=None, want_traj=True,
-                  prefix="orc"):
+                  prefix="orc", engine="mt"):
     dp, dp_u = _arr(depth, np.uint32)
     ms, _ = _arr(model_seeds, np.uint64)
     dmax = int(dp.max()) if dp is not None and len(dp) else dp_u
@@ -153,14 +181,19 @@ def mold_rollouts(lib, n, *, n_actions, depth, model_seed=0, model_pre_discard=0
         payoff = np.zeros(n, np.uint8)
         th = np.zeros(n, np.uint32)
         sums = np.zeros(8, np.uint64)
-        steps = lib.orc_mold_rollouts(n, n_actions, p(dp), dp_u, p(ms), model_seed, model_pre_discard, p(payoff),
-                                      p(traj), max(dmax, 1), p(th), p(sums))
+        lib.orc_set_engine_kind(1 if engine == "xs" else 0)
+        try:
+            steps = lib.orc_mold_rollouts(n, n_actions, p(dp), dp_u, p(ms), model_seed, model_pre_discard, p(payoff),
+                                          p(traj), max(dmax, 1), p(th), p(sums))
+        finally:
+            lib.orc_set_engine_kind(0)
         res.update(payoff=payoff, traj_hash=th, sums=sums)
     else:
         prow = np.zeros(n, np.float64)
         pcol = np.zeros(n, np.float64)
-        steps = lib.ref_mold_rollouts(n, n_actions, p(dp), dp_u, p(ms), model_seed, model_pre_discard, p(prow), p(pcol),
-                                      p(traj), max(dmax, 1))
+        fn = lib.ref_xs_mold_rollouts if engine == "xs" else lib.ref_mold_rollouts
+        steps = fn(n, n_actions, p(dp), dp_u, p(ms), model_seed, model_pre_discard, p(prow), p(pcol),
+                   p(traj), max(dmax, 1))
         res.update(payoff_row=prow, payoff_col=pcol)
     res["steps"] = steps
     return res

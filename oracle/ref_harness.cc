@@ -33,6 +33,7 @@
 #include <model/monte-carlo-model.hh>
 #include <state/random-tree.hh>
 #include <state/test-states.hh>
+#include <libpinyon/grow-lib.hh>
 
 #include <algorithm/tree-bandit/bandit/exp3.hh>
 #include <algorithm/tree-bandit/tree/off-policy.hh>
@@ -47,8 +48,9 @@ struct TraceSink {
 };
 thread_local TraceSink *g_sink = nullptr;
 
-struct TracedTree : RandomTree<> {
-    using Base = RandomTree<>::State;
+template <typename TL>
+struct TracedTreeT : RandomTree<TL> {
+    using Base = typename RandomTree<TL>::State;
     class State : public Base {
        public:
         using Base::Base;
@@ -69,8 +71,9 @@ struct TracedTree : RandomTree<> {
     };
 };
 
-struct TracedMold : MoldState<> {
-    using Base = MoldState<>::State;
+template <typename TL>
+struct TracedMoldT : MoldState<TL> {
+    using Base = typename MoldState<TL>::State;
     class State : public Base {
        public:
         using Base::Base;
@@ -90,6 +93,35 @@ struct TracedMold : MoldState<> {
     };
 };
 
+using TracedTree = TracedTreeT<RandomTreeFloatTypes>;
+using TracedMold = TracedMoldT<SimpleTypes>;
+
+// ---- the xor_shift PRNG (src/types/random.hh:66-121) as a type list.  The class as shipped fails IsPRNG
+// (types.hh:165-190 wants random_seed()), so no reference type list can name it; the one missing member is added
+// here, exactly as a user would have to, and nothing else is touched.
+struct xor_shift_prng : xor_shift {
+    using xor_shift::xor_shift;
+    uint64_t random_seed() { return uniform_64(); }
+};
+using XsTreeTypes = DefaultTypes<double, int, int, double, ConstantSum<1, 1>::Value, std::vector, Matrix, std::mutex,
+                                 uint64_t, xor_shift_prng>;
+using XsMoldTypes = DefaultTypes<double, int, int, double, PairReal, std::vector, Matrix, std::mutex, uint64_t, xor_shift_prng>;
+static_assert(IsTypeList<XsTreeTypes>);
+
+// xor_shift keeps its 64-bit state private: read it through the explicit-instantiation access rule.
+template <typename Tag, typename Tag::type Member>
+struct PrivateAccess {
+    friend typename Tag::type harness_get(Tag) { return Member; }
+};
+struct XsStateTag {
+    using type = uint64_t xor_shift::*;
+    friend type harness_get(XsStateTag);
+};
+template struct PrivateAccess<XsStateTag, &xor_shift::state>;
+inline uint64_t xs_state_of(const xor_shift &d) { return d.*harness_get(XsStateTag{}); }
+
+int g_growth = 0;  // 0: default growth functions; 1: GrowLib::alternating_constant_actions as actions_func
+
 using TreeMC = MonteCarloModel<TracedTree>;
 using MoldMC = MonteCarloModel<TracedMold>;
 using PlainTreeMC = MonteCarloModel<RandomTree<>>;
@@ -100,6 +132,94 @@ static_assert(IsBatchModelTypes<PlainTreeMC>);
 static_assert(IsSingleModelTypes<PlainMoldMC>);
 
 inline uint8_t payoff_code(double row_value) { return static_cast<uint8_t>(row_value * 2.0); }
+
+template <typename TL>
+uint64_t tree_rollouts(uint64_t n, const uint64_t *state_seeds, uint64_t state_seed_u, const uint32_t *state_pre_discards,
+                       uint32_t state_pre_discard_u, const uint64_t *transition_seeds, uint64_t transition_seed_u,
+                       const uint32_t *depths, uint32_t depth_u, const int32_t *payoff_biases, int32_t payoff_bias_u,
+                       uint32_t rows, uint32_t cols, uint32_t transitions, int thr_p, int thr_q, const uint64_t *model_seeds,
+                       uint64_t model_seed_u, uint64_t model_pre_discard, uint8_t *payoff_x2, uint8_t *traj,
+                       uint32_t traj_depth_max, uint64_t *state_after_ctor) {
+    using Traced = TracedTreeT<TL>;
+    using MC = MonteCarloModel<Traced>;
+    using PRNG = typename TL::PRNG;
+    using BaseState = typename RandomTree<TL>::State;
+    typename MC::Model shared_model{PRNG{model_seed_u}};
+    shared_model.device.discard(model_pre_discard);
+    uint64_t total_steps = 0;
+    TraceSink sink;
+    g_sink = &sink;
+
+    const bool uniform_root = !state_seeds && !state_pre_discards && !depths;
+    std::unique_ptr<typename Traced::State> root_cache;
+
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint64_t sseed = state_seeds ? state_seeds[i] : state_seed_u;
+        const uint32_t spre = state_pre_discards ? state_pre_discards[i] : state_pre_discard_u;
+        const uint32_t depth = depths ? depths[i] : depth_u;
+        if (!uniform_root || !root_cache) {
+            PRNG d{sseed};
+            d.discard(spre);
+            if (g_growth == 1)  // GrowLib::alternating_constant_actions as actions_func (random-tree.hh:43-57)
+                root_cache = std::make_unique<typename Traced::State>(BaseState{
+                    d, depth, rows, cols, transitions, Rational<>{thr_p, thr_q}, &BaseState::depth_bound_default,
+                    &GrowLib::alternating_constant_actions<BaseState>, &BaseState::payoff_bias_default});
+            else
+                root_cache = std::make_unique<typename Traced::State>(d, depth, rows, cols, transitions, Rational<>{thr_p, thr_q});
+        }
+        if constexpr (std::is_base_of_v<xor_shift, PRNG>)
+            if (state_after_ctor) state_after_ctor[i] = xs_state_of(root_cache->device);
+        typename Traced::State state{*root_cache};
+        state.randomize_transition(transition_seeds ? transition_seeds[i] : transition_seed_u);
+        state.payoff_bias = payoff_biases ? payoff_biases[i] : payoff_bias_u;
+
+        sink.traj = traj ? traj + 3 * static_cast<size_t>(traj_depth_max) * i : nullptr;
+        sink.steps = 0;
+        typename MC::ModelOutput out;
+        if (model_seeds) {
+            typename MC::Model model{PRNG{model_seeds[i]}};
+            model.inference(std::move(state), out);
+        } else {
+            shared_model.inference(std::move(state), out);
+        }
+        total_steps += sink.steps;
+        if (payoff_x2) payoff_x2[i] = payoff_code(out.value.get_row_value());
+    }
+    g_sink = nullptr;
+    return total_steps;
+}
+
+template <typename TL>
+uint64_t mold_rollouts(uint64_t n, uint32_t n_actions, const uint32_t *depths, uint32_t depth_u, const uint64_t *model_seeds,
+                       uint64_t model_seed_u, uint64_t model_pre_discard, double *payoff_row, double *payoff_col, uint8_t *traj,
+                       uint32_t traj_depth_max) {
+    using Traced = TracedMoldT<TL>;
+    using MC = MonteCarloModel<Traced>;
+    using PRNG = typename TL::PRNG;
+    typename MC::Model shared_model{PRNG{model_seed_u}};
+    shared_model.device.discard(model_pre_discard);
+    uint64_t total_steps = 0;
+    TraceSink sink;
+    g_sink = &sink;
+    for (uint64_t i = 0; i < n; ++i) {
+        const uint32_t depth = depths ? depths[i] : depth_u;
+        typename Traced::State state{n_actions, depth};
+        sink.traj = traj ? traj + 3 * static_cast<size_t>(traj_depth_max) * i : nullptr;
+        sink.steps = 0;
+        typename MC::ModelOutput out;
+        if (model_seeds) {
+            typename MC::Model model{PRNG{model_seeds[i]}};
+            model.inference(std::move(state), out);
+        } else {
+            shared_model.inference(std::move(state), out);
+        }
+        total_steps += sink.steps;
+        if (payoff_row) payoff_row[i] = out.value.get_row_value();
+        if (payoff_col) payoff_col[i] = out.value.get_col_value();
+    }
+    g_sink = nullptr;
+    return total_steps;
+}
 
 }  // namespace
 
@@ -151,73 +271,44 @@ uint64_t ref_random_tree_rollouts(uint64_t n, const uint64_t *state_seeds, uint6
                                   int thr_p, int thr_q, const uint64_t *model_seeds, uint64_t model_seed_u,
                                   uint64_t model_pre_discard, uint8_t *payoff_x2, uint8_t *traj,
                                   uint32_t traj_depth_max) {
-    TreeMC::Model shared_model{prng{model_seed_u}};
-    shared_model.device.discard(model_pre_discard);
-    uint64_t total_steps = 0;
-    TraceSink sink;
-    g_sink = &sink;
-
-    const bool uniform_root = !state_seeds && !state_pre_discards && !depths;
-    std::unique_ptr<TracedTree::State> root_cache;
-
-    for (uint64_t i = 0; i < n; ++i) {
-        const uint64_t sseed = state_seeds ? state_seeds[i] : state_seed_u;
-        const uint32_t spre = state_pre_discards ? state_pre_discards[i] : state_pre_discard_u;
-        const uint32_t depth = depths ? depths[i] : depth_u;
-        if (!uniform_root || !root_cache) {
-            prng d{sseed};
-            d.discard(spre);
-            root_cache = std::make_unique<TracedTree::State>(d, depth, rows, cols, transitions,
-                                                             Rational<>{thr_p, thr_q});
-        }
-        TracedTree::State state{*root_cache};
-        state.randomize_transition(transition_seeds ? transition_seeds[i] : transition_seed_u);
-        state.payoff_bias = payoff_biases ? payoff_biases[i] : payoff_bias_u;
-
-        sink.traj = traj ? traj + 3 * static_cast<size_t>(traj_depth_max) * i : nullptr;
-        sink.steps = 0;
-        TreeMC::ModelOutput out;
-        if (model_seeds) {
-            TreeMC::Model model{prng{model_seeds[i]}};
-            model.inference(std::move(state), out);
-        } else {
-            shared_model.inference(std::move(state), out);
-        }
-        total_steps += sink.steps;
-        if (payoff_x2) payoff_x2[i] = payoff_code(out.value.get_row_value());
-    }
-    g_sink = nullptr;
-    return total_steps;
+    return tree_rollouts<RandomTreeFloatTypes>(n, state_seeds, state_seed_u, state_pre_discards, state_pre_discard_u,
+                                               transition_seeds, transition_seed_u, depths, depth_u, payoff_biases,
+                                               payoff_bias_u, rows, cols, transitions, thr_p, thr_q, model_seeds,
+                                               model_seed_u, model_pre_discard, payoff_x2, traj, traj_depth_max, nullptr);
 }
+
+// The same over the xor_shift type list.  Seeds are engine STATES (xor_shift(seed): state = seed, random.hh:72);
+// state_after_ctor (nullable) receives each root's engine state as the constructor left it — what the CUDA library's
+// batch carries for an xor_shift state.
+uint64_t ref_xs_random_tree_rollouts(uint64_t n, const uint64_t *state_seeds, uint64_t state_seed_u,
+                                     const uint32_t *state_pre_discards, uint32_t state_pre_discard_u,
+                                     const uint64_t *transition_seeds, uint64_t transition_seed_u,
+                                     const uint32_t *depths, uint32_t depth_u, const int32_t *payoff_biases,
+                                     int32_t payoff_bias_u, uint32_t rows, uint32_t cols, uint32_t transitions,
+                                     int thr_p, int thr_q, const uint64_t *model_seeds, uint64_t model_seed_u,
+                                     uint64_t model_pre_discard, uint8_t *payoff_x2, uint8_t *traj,
+                                     uint32_t traj_depth_max, uint64_t *state_after_ctor) {
+    return tree_rollouts<XsTreeTypes>(n, state_seeds, state_seed_u, state_pre_discards, state_pre_discard_u,
+                                      transition_seeds, transition_seed_u, depths, depth_u, payoff_biases, payoff_bias_u,
+                                      rows, cols, transitions, thr_p, thr_q, model_seeds, model_seed_u, model_pre_discard,
+                                      payoff_x2, traj, traj_depth_max, state_after_ctor);
+}
+
+void ref_set_growth(int growth) { g_growth = growth; }
 
 // MoldState rollouts (test-states.hh:13-67; benchmark/mold-state.cc:3-12).
 // payoff_row/payoff_col receive the (never-set, hence 0,0) PairReal payoff.
 uint64_t ref_mold_rollouts(uint64_t n, uint32_t n_actions, const uint32_t *depths, uint32_t depth_u,
                            const uint64_t *model_seeds, uint64_t model_seed_u, uint64_t model_pre_discard,
                            double *payoff_row, double *payoff_col, uint8_t *traj, uint32_t traj_depth_max) {
-    MoldMC::Model shared_model{prng{model_seed_u}};
-    shared_model.device.discard(model_pre_discard);
-    uint64_t total_steps = 0;
-    TraceSink sink;
-    g_sink = &sink;
-    for (uint64_t i = 0; i < n; ++i) {
-        const uint32_t depth = depths ? depths[i] : depth_u;
-        TracedMold::State state{n_actions, depth};
-        sink.traj = traj ? traj + 3 * static_cast<size_t>(traj_depth_max) * i : nullptr;
-        sink.steps = 0;
-        MoldMC::ModelOutput out;
-        if (model_seeds) {
-            MoldMC::Model model{prng{model_seeds[i]}};
-            model.inference(std::move(state), out);
-        } else {
-            shared_model.inference(std::move(state), out);
-        }
-        total_steps += sink.steps;
-        if (payoff_row) payoff_row[i] = out.value.get_row_value();
-        if (payoff_col) payoff_col[i] = out.value.get_col_value();
-    }
-    g_sink = nullptr;
-    return total_steps;
+    return mold_rollouts<SimpleTypes>(n, n_actions, depths, depth_u, model_seeds, model_seed_u, model_pre_discard, payoff_row,
+                                      payoff_col, traj, traj_depth_max);
+}
+uint64_t ref_xs_mold_rollouts(uint64_t n, uint32_t n_actions, const uint32_t *depths, uint32_t depth_u,
+                              const uint64_t *model_seeds, uint64_t model_seed_u, uint64_t model_pre_discard,
+                              double *payoff_row, double *payoff_col, uint8_t *traj, uint32_t traj_depth_max) {
+    return mold_rollouts<XsMoldTypes>(n, n_actions, depths, depth_u, model_seeds, model_seed_u, model_pre_discard, payoff_row,
+                                      payoff_col, traj, traj_depth_max);
 }
 
 // CPU baseline timing: the reference's untraced MonteCarloModel, `threads`

@@ -25,6 +25,10 @@ PCU_MEM_DEVICE = 1
 PCU_MODEL_STREAM = 0
 PCU_MODEL_PER_ROLLOUT = 1
 PCU_MODEL_WORDS = 2
+PCU_ENGINE_MT19937 = 0
+PCU_ENGINE_XOR_SHIFT = 1
+PCU_GROWTH_DEFAULT = 0
+PCU_GROWTH_ALTERNATING_CONSTANT = 1
 
 HASH_INIT = 2166136261
 HASH_MUL = 16777619
@@ -40,13 +44,13 @@ EXPORTS = [
     "pcu_create", "pcu_destroy", "pcu_last_error", "pcu_version", "pcu_set_stream", "pcu_kernel_launches", "pcu_last_kernel_ms",
     "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next", "pcu_mt_discard_family",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
-    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup", "pcu_visible_devices", "pcu_mt_take_raw",
+    "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup", "pcu_visible_devices", "pcu_mt_take_raw", "pcu_xs_discard",
 ]
 
 
 class ModelRng(C.Structure):
     _fields_ = [("mode", C.c_int32), ("mt_x", C.c_void_p), ("mt_p", C.c_void_p), ("seeds", C.c_void_p),
-                ("words", C.c_void_p)]
+                ("words", C.c_void_p), ("engine", C.c_uint32), ("xs_state", C.c_void_p)]
 
 
 class RtBatch(C.Structure):
@@ -58,7 +62,7 @@ class RtBatch(C.Structure):
         ("depth", C.c_void_p), ("depth_u", C.c_uint16),
         ("payoff_bias", C.c_void_p), ("payoff_bias_u", C.c_int32),
         ("rows", C.c_uint32), ("cols", C.c_uint32), ("transitions", C.c_uint32),
-        ("thr_p", C.c_int32), ("thr_q", C.c_int32),
+        ("thr_p", C.c_int32), ("thr_q", C.c_int32), ("growth", C.c_uint32),
     ]
 
 
@@ -116,6 +120,8 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_mt_discard.argtypes = [vp, vp, u64]
     lib.pcu_mt_discard_family.argtypes = [vp, vp, u64, u64]
     lib.pcu_mt_take_raw.argtypes = [vp, vp, u64, vp]
+    lib.pcu_xs_discard.argtypes = [u64, u64]
+    lib.pcu_xs_discard.restype = u64
     lib.pcu_mt_next.argtypes = [vp, vp]
     lib.pcu_mt_next.restype = u32
     lib.pcu_rollout_random_tree.argtypes = [vp, C.POINTER(RtBatch), C.POINTER(ModelRng), C.POINTER(Out)]
@@ -271,8 +277,17 @@ class Context:
         return arr
 
     # -- the hot path ---------------------------------------------------------------
-    def _rng(self, engine, model_seeds, model_words=None):
+    def _rng(self, engine, model_seeds, model_words=None, xs_state=None, xor_shift=False):
         r = ModelRng()
+        if xs_state is not None or xor_shift:  # Pinyon's xor_shift PRNG: xs_state = np.uint64[1] (mode S) or seeds (mode P)
+            r.engine = PCU_ENGINE_XOR_SHIFT
+            if xs_state is not None:
+                r.mode = PCU_MODEL_STREAM
+                r.xs_state = xs_state.ctypes.data
+            else:
+                r.mode = PCU_MODEL_PER_ROLLOUT
+                r.seeds = _ptr(model_seeds)
+            return r
         if model_words is not None:
             r.mode = PCU_MODEL_WORDS
             r.words = _ptr(model_words)
@@ -302,7 +317,7 @@ class Context:
     def rollout_random_tree(self, n, *, rows, cols, transitions=1, thr=(0, 1), depth=None, state_seed=0,
                             state_pos=None, transition_seed=0, payoff_bias=0, engine: Engine = None,
                             model_seeds=None, payoff=None, traj=None, traj_stride=0, traj_hash=None, sums=None,
-                            payoff_packed=None, model_words=None):
+                            payoff_packed=None, model_words=None, growth=0, xs_state=None, xor_shift=False):
         """pcu_rollout_random_tree.  Scalar arguments are batch-uniform; numpy arrays
         (host) or torch CUDA tensors (device) are per-rollout.  state_pos defaults to a
         freshly constructed root: 2*rows*cols*transitions draws."""
@@ -329,14 +344,16 @@ class Context:
         put("payoff_bias", payoff_bias, np.int32)
         b.rows, b.cols, b.transitions = rows, cols, transitions
         b.thr_p, b.thr_q = thr
+        b.growth = growth
         device = _is_device(*arrays, model_seeds, model_words, payoff, traj, traj_hash, sums, payoff_packed)
         b.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
-        r = self._rng(engine, model_seeds, model_words)
+        r = self._rng(engine, model_seeds, model_words, xs_state, xor_shift)
         o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_random_tree(self.h, C.byref(b), C.byref(r), C.byref(o)))
 
     def rollout_mold(self, n, *, n_actions, depth, engine: Engine = None, model_seeds=None, payoff=None, traj=None,
-                     traj_stride=0, traj_hash=None, sums=None, payoff_packed=None, model_words=None):
+                     traj_stride=0, traj_hash=None, sums=None, payoff_packed=None, model_words=None, xs_state=None,
+                     xor_shift=False):
         b = MoldBatch()
         b.n = n
         arrays = []
@@ -349,6 +366,6 @@ class Context:
         b.n_actions = n_actions
         device = _is_device(*arrays, model_seeds, model_words, payoff, traj, traj_hash, sums, payoff_packed)
         b.mem = PCU_MEM_DEVICE if device else PCU_MEM_HOST
-        r = self._rng(engine, model_seeds, model_words)
+        r = self._rng(engine, model_seeds, model_words, xs_state, xor_shift)
         o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_mold(self.h, C.byref(b), C.byref(r), C.byref(o)))

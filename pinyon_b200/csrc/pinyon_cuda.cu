@@ -51,7 +51,7 @@ constexpr int PIN_BASE_WINDOW = 1024; /* word offset in pin_small of the staged 
 
 enum BufId {
     B_STATE_SEED, B_STATE_POS, B_TSEED, B_DEPTH, B_BIAS, B_MSEED, B_PAYOFF, B_TRAJ, B_HASH, B_SUMS,
-    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_SEEDED, B_PACKED, B_PAYTMP, B_WORDS,
+    B_CKPT, B_CODES, B_STEPOFF, B_TAB, B_FQ, B_ENDWIN, B_SCRATCH, B_BOUND, B_L397, B_SEEDED, B_PACKED, B_PAYTMP, B_WORDS, B_XSPOW,
     B_COUNT
 };
 
@@ -100,6 +100,7 @@ struct pcu_ctx {
     } tab_key;
     /* cached fq table */
     uint32_t fq_w = 0;
+    bool xs_pow_ready = false; /* buf[B_XSPOW] holds the powers of the xor_shift step matrix */
     MtJump jump; /* host polynomials + device images for the model-stream jump-ahead */
     /* statistics of the last rollout call (pcu_get_stat) */
     uint64_t last_chunk = 0, last_streams = 0;
@@ -1031,9 +1032,11 @@ int run_small(pcu_ctx *ctx, SmallParams &SP, uint32_t n, pcu_model_rng *rng, con
 int check_common(pcu_ctx *ctx, const void *batch, const pcu_model_rng *rng, const pcu_out *out) {
     if (!ctx) return PCU_ERR_INVALID;
     if (!batch || !rng || !out) return fail(ctx, PCU_ERR_INVALID, "null batch, rng or out");
-    if (rng->mode == PCU_MODEL_STREAM) {
+    if (rng->mode == PCU_MODEL_STREAM && rng->engine != PCU_ENGINE_XOR_SHIFT) {
         if (!rng->mt_x || !rng->mt_p) return fail(ctx, PCU_ERR_INVALID, "mode S needs mt_x and mt_p");
         if (*rng->mt_p > MT_N) return fail(ctx, PCU_ERR_INVALID, "mt_p %u out of range", *rng->mt_p);
+    } else if (rng->mode == PCU_MODEL_STREAM) {
+        /* xor_shift: checked below */
     } else if (rng->mode == PCU_MODEL_PER_ROLLOUT) {
         if (!rng->seeds) return fail(ctx, PCU_ERR_INVALID, "mode P needs seeds");
     } else if (rng->mode == PCU_MODEL_WORDS) {
@@ -1043,6 +1046,12 @@ int check_common(pcu_ctx *ctx, const void *batch, const pcu_model_rng *rng, cons
         return fail(ctx, PCU_ERR_INVALID, "unknown model rng mode %d", rng->mode);
     }
     if (out->mem != PCU_MEM_HOST && out->mem != PCU_MEM_DEVICE) return fail(ctx, PCU_ERR_INVALID, "bad out->mem");
+    if (rng->engine == PCU_ENGINE_XOR_SHIFT) {
+        if (rng->mode == PCU_MODEL_WORDS) return fail(ctx, PCU_ERR_UNSUPPORTED, "mode W is not offered for xor_shift");
+        if (rng->mode == PCU_MODEL_STREAM && !rng->xs_state) return fail(ctx, PCU_ERR_INVALID, "xor_shift mode S needs xs_state");
+    } else if (rng->engine != PCU_ENGINE_MT19937) {
+        return fail(ctx, PCU_ERR_INVALID, "unknown engine %u", rng->engine);
+    }
     return PCU_OK;
 }
 
@@ -1381,6 +1390,124 @@ int launch_leaf(pcu_ctx *ctx, const LeafParams &L) {
     return PCU_OK;
 }
 
+/* ---- the variant path (thread.cuh): xor_shift type lists and grow-lib growth functions */
+
+/* Columns of A^(2^j), j = 0..63, for the xor_shift step matrix A over GF(2): pw[64 j + b] = A^(2^j) e_b. */
+const uint64_t *xs_powers() {
+    static uint64_t pw[64 * 64];
+    static bool ready = false;
+    static std::mutex mu;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!ready) {
+        for (int b = 0; b < 64; ++b) pw[b] = xs_step(1ull << b); /* the step is linear: A e_b */
+        for (int j = 1; j < 64; ++j)
+            for (int b = 0; b < 64; ++b) { /* A^(2^j) e_b = A^(2^(j-1)) (A^(2^(j-1)) e_b) */
+                const uint64_t v = pw[64 * (j - 1) + b];
+                uint64_t y = 0;
+                for (int c = 0; c < 64; ++c)
+                    if ((v >> c) & 1) y ^= pw[64 * (j - 1) + c];
+                pw[64 * j + b] = y;
+            }
+        ready = true;
+    }
+    return pw;
+}
+
+uint64_t host_xs_discard(uint64_t s, uint64_t k) {
+    const uint64_t *pw = xs_powers();
+    for (int j = 0; k; ++j, k >>= 1) {
+        if (!(k & 1)) continue;
+        uint64_t y = 0;
+        for (int b = 0; b < 64; ++b)
+            if ((s >> b) & 1) y ^= pw[64 * j + b];
+        s = y;
+    }
+    return s;
+}
+
+/* MT19937 mode S for the variant kernel: the model stream itself, four engine outputs per step, into B_WORDS
+ * (the action counts change from step to step, so the generator cannot reduce the draws itself). */
+int gen_words(pcu_ctx *ctx, uint64_t total_steps, pcu_model_rng *rng) {
+    const uint64_t slots = (uint64_t)ctx->sms * (ctx->streams_per_sm ? ctx->streams_per_sm : 4);
+    const uint64_t chunk = pick_chunk(total_steps ? total_steps : 1, slots, 4096);
+    uint64_t streams = (total_steps + chunk - 1) / chunk;
+    if (streams == 0) streams = 1;
+    int rc = make_checkpoints(ctx, rng->mt_x, *rng->mt_p, 0, streams, 4ull * chunk);
+    if (rc) return rc;
+    CU(ctx->buf[B_WORDS].ensure(16 * (total_steps + 1)));
+    Gen2Params G;
+    memset(&G, 0, sizeof(G));
+    G.total_steps = total_steps;
+    G.chunk_steps = chunk;
+    G.streams = (uint32_t)streams;
+    G.checkpoints = reinterpret_cast<const uint32_t *>(ctx->buf[B_CKPT].p);
+    G.codes = ctx->buf[B_WORDS].p;
+    G.end_window = reinterpret_cast<uint32_t *>(ctx->buf[B_ENDWIN].p);
+    if (total_steps == 0) return PCU_OK;
+    k_gen_words<<<(unsigned)((streams + 3) / 4), 128, 0, ctx->stream>>>(G);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    return fetch_end_window(ctx);
+}
+
+/* Shared by RandomTree and MoldState batches: everything the fast kernels do not take. */
+int run_variant(pcu_ctx *ctx, ThreadParams &P, int mem, const uint16_t *h_depth, const uint16_t *d_depth, pcu_model_rng *rng,
+                const pcu_out *out, OutDev &od, const char *path) {
+    int rc;
+    const uint64_t n = P.n;
+    const bool xs = rng->engine == PCU_ENGINE_XOR_SHIFT;
+    uint64_t total_steps = n * (uint64_t)P.depth_u;
+    if (rng->mode == PCU_MODEL_WORDS) {
+        WordsDev wd;
+        if ((rc = stage_words(ctx, mem, n, h_depth, d_depth, P.depth_u, rng, wd))) return rc;
+        P.model_src = TH_MODEL_WORDS;
+        P.words = wd.words;
+        P.words_raw = 1;
+        P.step_off = wd.step_off;
+        if ((rc = inputs_ready(ctx))) return rc;
+    } else {
+        if ((rc = inputs_ready(ctx))) return rc;
+        if (d_depth && rng->mode == PCU_MODEL_STREAM && (rc = scan_depths(ctx, d_depth, n, &P.step_off, &total_steps))) return rc;
+        if (rng->mode == PCU_MODEL_PER_ROLLOUT) {
+            P.model_src = TH_MODEL_SEEDS;
+        } else if (xs) {
+            if (!ctx->xs_pow_ready) {
+                CU(ctx->buf[B_XSPOW].ensure(sizeof(uint64_t) * 64 * 64));
+                CU(cudaMemcpyAsync(ctx->buf[B_XSPOW].p, xs_powers(), sizeof(uint64_t) * 64 * 64, cudaMemcpyHostToDevice, ctx->stream));
+                ctx->xs_pow_ready = true;
+            }
+            P.model_src = TH_MODEL_XS_STREAM;
+            P.xs_m0 = *rng->xs_state;
+            P.xs_pow = reinterpret_cast<const uint64_t *>(ctx->buf[B_XSPOW].p);
+        } else {
+            if ((rc = gen_words(ctx, total_steps, rng))) return rc;
+            P.model_src = TH_MODEL_WORDS;
+            P.words = reinterpret_cast<const uint32_t *>(ctx->buf[B_WORDS].p);
+            P.words_raw = 0;
+        }
+    }
+    if ((rc = pack_source(ctx, od, n, &P.payoff))) return rc;
+    P.traj = od.traj;
+    P.traj_stride = out->traj_stride;
+    P.traj_hash = od.hash;
+    P.sums = od.sums;
+    ctx->path = path;
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    if (xs)
+        k_thread<PCU_ENG_XORSHIFT><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(P);
+    else
+        k_thread<PCU_ENG_MT19937><<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(P);
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
+    ctx->launches++;
+    CU(cudaGetLastError());
+    if ((rc = pack_after(ctx, od, n, P.payoff))) return rc;
+    if ((rc = finish_all(ctx, out, n, od, rng))) return rc;
+    if (xs && rng->mode == PCU_MODEL_STREAM && !ctx->hint.no_sync) /* two draws per step (monte-carlo-model.hh:89-90) */
+        *rng->xs_state = host_xs_discard(*rng->xs_state, 2 * total_steps);
+    return PCU_OK;
+}
+
 /* One GPU's share of the work: everything below runs on ctx->device. */
 int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_out *out) {
     int rc = check_common(ctx, b, rng, out);
@@ -1399,18 +1526,20 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
                     "transitions > 8: the reference's Rational<int> sum p/10^T (random-tree.hh:165-184, rational.hh:82-87) "
                     "overflows int once 10^(T-1) * sum(n_k) >= 2^31, so its results are undefined behaviour there");
     if (b->thr_q <= 0 || b->thr_p < 0) return fail(ctx, PCU_ERR_INVALID, "chance_threshold must be p/q with p >= 0, q > 0");
+    if (b->growth > PCU_GROWTH_ALTERNATING_CONSTANT) return fail(ctx, PCU_ERR_INVALID, "unknown growth %u", b->growth);
     if (!b->depth && b->depth_u == 0)
         return fail(ctx, PCU_ERR_INVALID, "depth_bound 0 never terminates in the reference (random-tree.hh:95-99)");
     const uint64_t n = b->n;
     const uint32_t T = b->transitions;
     const uint32_t gen_words = 2 * b->rows * b->cols * T;
-    if (!b->state_pos && b->state_pos_u < gen_words)
+    const bool is_variant = rng->engine == PCU_ENGINE_XOR_SHIFT || b->growth != PCU_GROWTH_DEFAULT;
+    if (rng->engine != PCU_ENGINE_XOR_SHIFT && !b->state_pos && b->state_pos_u < gen_words)
         return fail(ctx, PCU_ERR_INVALID, "state_pos %u < 2*rows*cols*transitions = %u", b->state_pos_u, gen_words);
     if (out->traj && out->traj_stride < (b->depth ? 1u : b->depth_u))
         return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
     CU(cudaSetDevice(ctx->device));
     if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST && !out->payoff_packed2 &&
-        !ctx->hint.no_sync && rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
+        !ctx->hint.no_sync && rng->mode == PCU_MODEL_STREAM && !is_variant && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
         static thread_local SmallParams SP; /* ~3.6 KB: kept off the stack of recursive searches */
         memset(&SP.w, 0, sizeof(SP.w));
         SP.w.rows = b->rows;
@@ -1450,6 +1579,39 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+    if (rng->engine == PCU_ENGINE_XOR_SHIFT || b->growth != PCU_GROWTH_DEFAULT) {
+        ThreadParams TP;
+        memset(&TP, 0, sizeof(TP));
+        TP.n = n;
+        TP.kind = KIND_TREE;
+        TP.rows = b->rows;
+        TP.cols = b->cols;
+        TP.T = T;
+        TP.growth = b->growth;
+        TP.thr_p = b->thr_p;
+        TP.thr_q = b->thr_q;
+        TP.state_seed = d_sseed;
+        TP.state_seed_u = b->state_seed_u;
+        TP.state_pos = d_pos;
+        TP.state_pos_u = b->state_pos_u;
+        TP.tseed = d_tseed;
+        TP.tseed_u = b->transition_seed_u;
+        TP.depth = d_depth;
+        TP.depth_u = b->depth_u;
+        TP.bias = d_bias;
+        TP.bias_u = b->payoff_bias_u;
+        TP.model_seeds = d_mseed;
+        if (T > 1 && (rc = upload_fq(ctx, T, &TP.fq, &TP.fq_w))) return rc;
+        if (b->state_pos && rng->engine != PCU_ENGINE_XOR_SHIFT) { /* positions are range-checked on every path */
+            uint64_t lw, ld;
+            uint32_t pmin = 0, pmax = 0;
+            if ((rc = inputs_ready(ctx))) return rc;
+            if ((rc = lane_bound(ctx, n, d_pos, b->state_pos_u, d_depth, b->depth_u, gen_words, 0, &lw, &ld, &pmin, &pmax))) return rc;
+            if (pmin < gen_words) return fail(ctx, PCU_ERR_INVALID, "a state_pos is below 2*rows*cols*transitions");
+        }
+        return run_variant(ctx, TP, b->mem, b->mem == PCU_MEM_HOST ? b->depth : nullptr, d_depth, rng, out, od,
+                           rng->engine == PCU_ENGINE_XOR_SHIFT ? "thread_tree_xs" : "thread_tree_growth");
+    }
     WordsDev wd;
     if (rng->mode == PCU_MODEL_WORDS && (rc = stage_words(ctx, b->mem, n, b->mem == PCU_MEM_HOST ? b->depth : nullptr,
                                                           d_depth, b->depth_u, rng, wd)))
@@ -1668,9 +1830,10 @@ int rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_
     if (out->traj && out->traj_stride < (b->depth ? 1u : b->depth_u))
         return fail(ctx, PCU_ERR_INVALID, "traj_stride smaller than depth");
     const uint64_t n = b->n;
+    const bool is_variant = rng->engine == PCU_ENGINE_XOR_SHIFT;
     CU(cudaSetDevice(ctx->device));
     if (ctx->small_path && !ctx->force_general && n >= 1 && n <= 32 && b->mem == PCU_MEM_HOST && !out->payoff_packed2 &&
-        !ctx->hint.no_sync && rng->mode == PCU_MODEL_STREAM && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
+        !ctx->hint.no_sync && rng->mode == PCU_MODEL_STREAM && !is_variant && (!out->traj || (size_t)n * out->traj_stride * 3 <= PIN_OUT_BYTES - PIN_OUT_TRAJ)) {
         static thread_local SmallParams SP;
         memset(&SP.w, 0, sizeof(SP.w));
         SP.w.rows = SP.w.cols = b->n_actions;
@@ -1690,6 +1853,18 @@ int rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng, pcu_
     if ((rc = stage_in(ctx, b->mem, b->depth, n, B_DEPTH, &d_depth))) return rc;
     if (rng->mode == PCU_MODEL_PER_ROLLOUT)
         if ((rc = stage_in(ctx, b->mem, rng->seeds, n, B_MSEED, &d_mseed))) return rc;
+    if (is_variant) {
+        ThreadParams TP;
+        memset(&TP, 0, sizeof(TP));
+        TP.n = n;
+        TP.kind = KIND_MOLD;
+        TP.rows = TP.cols = b->n_actions;
+        TP.T = 1;
+        TP.depth = d_depth;
+        TP.depth_u = b->depth_u;
+        TP.model_seeds = d_mseed;
+        return run_variant(ctx, TP, b->mem, b->mem == PCU_MEM_HOST ? b->depth : nullptr, d_depth, rng, out, od, "thread_mold_xs");
+    }
     WordsDev wd;
     if (rng->mode == PCU_MODEL_WORDS && (rc = stage_words(ctx, b->mem, n, b->mem == PCU_MEM_HOST ? b->depth : nullptr,
                                                           d_depth, b->depth_u, rng, wd)))
@@ -1983,8 +2158,9 @@ int multi_rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, 
     int rc = check_common(ctx, b, rng, out);
     if (rc) return rc;
     ctx->err.clear();
-    if (M.kids.size() == 1 || b->mem != PCU_MEM_HOST || out->mem != PCU_MEM_HOST || b->n < M.min_rollouts) {
-        /* small batches, and batches that already live on one GPU, stay on the first one */
+    if (M.kids.size() == 1 || b->mem != PCU_MEM_HOST || out->mem != PCU_MEM_HOST || b->n < M.min_rollouts ||
+        rng->engine != PCU_ENGINE_MT19937 || b->growth != PCU_GROWTH_DEFAULT) {
+        /* small batches, batches that already live on one GPU and the variant type lists stay on the first one */
         rc = rollout_tree(M.kids[0], b, rng, out);
         ctx->err = M.kids[0]->err;
         ctx->path = M.kids[0]->path;
@@ -2030,7 +2206,7 @@ int multi_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *b, pcu_model_rng *rng
     if (rc) return rc;
     ctx->err.clear();
     if (M.kids.size() == 1 || b->mem != PCU_MEM_HOST || out->mem != PCU_MEM_HOST || b->n < M.min_rollouts ||
-        (!b->depth && b->depth_u == 0)) {
+        (!b->depth && b->depth_u == 0) || rng->engine != PCU_ENGINE_MT19937) {
         rc = rollout_mold(M.kids[0], b, rng, out);
         ctx->err = M.kids[0]->err;
         ctx->path = M.kids[0]->path;
@@ -2125,6 +2301,8 @@ int pcu_create_multi(const int *device_ids, int n, pcu_ctx **out) {
     *out = ctx;
     return PCU_OK;
 }
+
+uint64_t pcu_xs_discard(uint64_t state, uint64_t n) { return host_xs_discard(state, n); }
 
 int pcu_visible_devices(void) {
     int count = 0, ok = 0;

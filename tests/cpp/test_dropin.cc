@@ -38,6 +38,13 @@ using GpuMold = PinyonCuda::MonteCarloModel<MoldState<>>;
 using GpuTreePolicy = PinyonCuda::MonteCarloModel<RandomTree<>, true>;
 using BatchedTree = PinyonCuda::BatchedMonteCarloModel<RandomTree<>>;
 using BatchedMold = PinyonCuda::BatchedMonteCarloModel<MoldState<>>;
+// ---- variants: a type list over Pinyon's xor_shift PRNG (with the member IsPRNG misses added)
+using XsTypes = DefaultTypes<double, int, int, double, ConstantSum<1, 1>::Value, std::vector, Matrix, std::mutex, uint64_t,
+                             PinyonCuda::xor_shift_prng>;
+using RefXsTree = MonteCarloModel<RandomTree<XsTypes>>;
+using GpuXsTree = PinyonCuda::MonteCarloModel<RandomTree<XsTypes>>;
+static_assert(IsTypeList<XsTypes>);
+static_assert(IsValueModelTypes<GpuXsTree> && IsSingleModelTypes<GpuXsTree> && IsBatchModelTypes<GpuXsTree>);
 
 // ---- the concepts every caller constrains its model with (src/model/model.hh:8-79)
 static_assert(IsValueModelTypes<GpuTree>);
@@ -469,6 +476,77 @@ static void test_batched_tree_bandit(size_t threads, size_t fibers, size_t itera
     std::printf("batching adapter ok\n");
 }
 
+// Variants: the xor_shift type list, and RandomTree states grown with GrowLib::alternating_constant_actions, through the
+// drop-in model against the reference's own MonteCarloModel over the same type list (single and batched inference,
+// mid-tree leaves, model engine in lock-step).
+template <typename Ref, typename Gpu, typename MakeState>
+static void variant_case(const char *name, MakeState make_root, uint64_t model_seed) {
+    using State = typename Ref::State;
+    using PRNG = typename Ref::PRNG;
+    const State root = make_root();
+    typename Ref::Model ref{PRNG{model_seed}};
+    typename Gpu::Model gpu{PRNG{model_seed}};
+    for (int i = 0; i < 25; ++i) { /* single leaves */
+        typename Ref::ModelOutput a;
+        typename Gpu::ModelOutput b;
+        ref.inference(State{root}, a);
+        gpu.inference(State{root}, b);
+        CHECK(same_value(a.value, b.value));
+    }
+    CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+    PRNG walker{model_seed + 17};
+    typename Ref::ModelBatchInput ref_in{};
+    typename Gpu::ModelBatchInput gpu_in{};
+    const int n = 1200;
+    for (int i = 0; i < n; ++i) { /* mid-tree leaves, some terminal */
+        State s{root};
+        if (i % 5 == 2) s.randomize_transition(walker);
+        const int down = walker.random_int(static_cast<int>(root.depth_bound) + 1);
+        for (int k = 0; k < down && !s.is_terminal(); ++k) {
+            s.apply_actions(walker.random_int(static_cast<int>(s.rows)), walker.random_int(static_cast<int>(s.cols)));
+            s.get_actions();
+        }
+        State s2{s};
+        ref.add_to_batch_input(std::move(s), ref_in);
+        gpu.add_to_batch_input(std::move(s2), gpu_in);
+    }
+    typename Ref::ModelBatchOutput ref_out{};
+    typename Gpu::ModelBatchOutput gpu_out{};
+    ref.inference(ref_in, ref_out);
+    gpu.inference(gpu_in, gpu_out);
+    int bad = 0;
+    for (int i = 0; i < n; ++i) {
+        typename Ref::ModelOutput a;
+        typename Gpu::ModelOutput b;
+        ref.get_output(a, ref_out, i);
+        gpu.get_output(b, gpu_out, i);
+        bad += !same_value(a.value, b.value);
+    }
+    CHECK(bad == 0);
+    CHECK(ref.device.uniform_64() == gpu.device.uniform_64());
+    std::printf("variant %s ok\n", name);
+}
+
+static void test_variants() {
+    using XsState = RandomTree<XsTypes>::State;
+    variant_case<RefXsTree, GpuXsTree>("xor_shift 3x3x1", [] { return XsState{PinyonCuda::xor_shift_prng{5}, 8, 3, 3, 1}; }, 77);
+    variant_case<RefXsTree, GpuXsTree>("xor_shift 4x3x3 thr 3/10",
+                                       [] { return XsState{PinyonCuda::xor_shift_prng{99}, 6, 4, 3, 3, Rational<>{3, 10}}; }, 1234567);
+    using St = RandomTree<>::State;
+    auto grown = [](uint64_t seed, size_t rows, size_t cols, size_t T) {
+        return St{prng{seed}, 7, rows, cols, T, Rational<>{0, 1}, &St::depth_bound_default,
+                  &GrowLib::alternating_constant_actions<St>, &St::payoff_bias_default};
+    };
+    variant_case<RefTree, GpuTree>("alternating_constant_actions 1x3x2", [&] { return grown(3, 1, 3, 2); }, 5);
+    variant_case<RefTree, GpuTree>("alternating_constant_actions 3x3x1", [&] { return grown(8, 3, 3, 1); }, 6);
+    using XsGrown = RandomTree<XsTypes>::State;
+    variant_case<RefXsTree, GpuXsTree>("xor_shift + alternating_constant_actions 3x1x2", [] {
+        return XsGrown{PinyonCuda::xor_shift_prng{41}, 6, 3, 1, 2, Rational<>{0, 1}, &XsGrown::depth_bound_default,
+                       &GrowLib::alternating_constant_actions<XsGrown>, &XsGrown::payoff_bias_default};
+    }, 9);
+    std::printf("variants ok\n");
+}
+
 // ONE model.inference(batch_in, batch_out) on a context that spans several GPUs (pcu_create_multi: contiguous
 // rollout-index shards, per-shard slices of the one model stream, NCCL all-reduce of the counters) must equal the same
 // call on one GPU byte for byte, including model.device afterwards (monte-carlo-model.hh:58-67).  With one GPU in the box
@@ -532,6 +610,7 @@ int main(int argc, char **argv) {
             test_search_callers();
             test_threaded_copies();
             test_batched_tree_bandit(4, 64, 200);
+            test_variants();
         } catch (const std::exception &e) {
             std::printf("FAIL exception: %s\n", e.what());
             ++g_failures;

@@ -91,6 +91,33 @@ def main():
                                 payoff_col=res["payoff_col"].tolist(), traj=res["traj"].reshape(N_TRAJ, -1).tolist(),
                                 steps=int(res["steps"])))
 
+    # variants: the xor_shift PRNG as a type list (with the one member IsPRNG misses added) and
+    # GrowLib::alternating_constant_actions as actions_func; mode S, ragged depths, per-rollout everything
+    doc["variants"] = []
+    rng = np.random.default_rng(77)
+    n = 40
+    for engine in ("mt", "xs"):
+        for growth in (0, 1):
+            if engine == "mt" and growth == 0:
+                continue
+            for rows, cols, T, thr in [(3, 3, 1, (0, 1)), (1, 3, 2, (3, 10)), (3, 1, 1, (0, 1)), (4, 5, 3, (1, 2))]:
+                arrays = dict(state_seed=rng.integers(1, 2**63, n).astype(np.uint64),
+                              state_pre_discard=rng.integers(0, 50, n).astype(np.uint32),
+                              transition_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+                              depth=rng.integers(1, 9, n).astype(np.uint32),
+                              payoff_bias=rng.integers(-2, 3, n).astype(np.int32))
+                res = loader.random_tree_rollouts(ref, n, prefix="ref", rows=rows, cols=cols, transitions=T, thr=thr,
+                                                  model_seed=12345, model_pre_discard=7, engine=engine, growth=growth, **arrays)
+                e = dict(engine=engine, growth=growth, rows=rows, cols=cols, transitions=T, thr=thr, n=n, model_seed=12345,
+                         model_pre_discard=7, arrays={k: [int(x) for x in v] for k, v in arrays.items()},
+                         payoff_x2=res["payoff"].tolist(), traj=res["traj"].reshape(n, -1).tolist(), steps=int(res["steps"]))
+                if engine == "xs":
+                    e["state_after_ctor"] = [int(x) for x in res["state_after_ctor"]]
+                doc["variants"].append(e)
+    d = rng.integers(0, 12, n).astype(np.uint32)
+    res = loader.mold_rollouts(ref, n, prefix="ref", n_actions=3, depth=d, model_seed=99, engine="xs")
+    doc["variants_mold_xs"] = dict(n=n, depth=[int(x) for x in d], model_seed=99, traj=res["traj"].reshape(n, -1).tolist())
+
     prng = {}
     for seed, disc in [(0, 0), (7, 620), (2**32 + 5, 1), (12345678901234, 100000)]:
         u64 = np.zeros(16, np.uint64)

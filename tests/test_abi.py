@@ -43,8 +43,9 @@ def test_struct_layouts_match_header():
       printf("%zu %zu %zu %zu\n", sizeof(pcu_model_rng), sizeof(pcu_rt_batch), sizeof(pcu_mold_batch), sizeof(pcu_out));
       printf("%zu %zu %zu %zu\n", offsetof(pcu_rt_batch, state_pos_u), offsetof(pcu_rt_batch, depth_u),
              offsetof(pcu_rt_batch, rows), offsetof(pcu_rt_batch, thr_q));
-      printf("%zu %zu %zu %zu\n", offsetof(pcu_out, traj_stride), offsetof(pcu_out, sums), offsetof(pcu_mold_batch, n_actions),
-             offsetof(pcu_out, payoff_packed2));
+      printf("%zu %zu %zu %zu %zu %zu %zu\n", offsetof(pcu_out, traj_stride), offsetof(pcu_out, sums), offsetof(pcu_mold_batch, n_actions),
+             offsetof(pcu_out, payoff_packed2), offsetof(pcu_rt_batch, growth), offsetof(pcu_model_rng, engine),
+             offsetof(pcu_model_rng, xs_state));
       return 0; }
     """
     with tempfile.TemporaryDirectory() as d:
@@ -57,7 +58,8 @@ def test_struct_layouts_match_header():
     assert vals[4:8] == [capi.RtBatch.state_pos_u.offset, capi.RtBatch.depth_u.offset, capi.RtBatch.rows.offset,
                          capi.RtBatch.thr_q.offset]
     assert vals[8:] == [capi.Out.traj_stride.offset, capi.Out.sums.offset, capi.MoldBatch.n_actions.offset,
-                        capi.Out.payoff_packed2.offset]
+                        capi.Out.payoff_packed2.offset, capi.RtBatch.growth.offset, capi.ModelRng.engine.offset,
+                        capi.ModelRng.xs_state.offset]
 
 
 def test_host_engine_matches_oracle(oracle):
@@ -157,6 +159,21 @@ def test_take_raw_is_the_untempered_stream(oracle):
         oracle.orc_mt_words(17, pre, n + 3, exp.ctypes.data)
         assert np.array_equal(temper(raw), exp[:n])
         assert [e.next() for _ in range(3)] == exp[n:].tolist()  # the engine continues behind the words taken
+
+
+def test_xor_shift_discard_matches_stepping(oracle):
+    """pcu_xs_discard (powers of the 64 x 64 step matrix over GF(2)) == xor_shift::discard (random.hh:107-111)."""
+    lib = capi.load_library()
+    oracle.orc_set_engine_kind(1)
+    try:
+        for state, n in ((1, 0), (5, 1), (0x9E3779B97F4A7C15, 1000), (12345, 2**20 + 3)):
+            out = np.zeros(1, np.uint64)
+            oracle.orc_prng_uniform_64(state, n, 1, out.ctypes.data)  # the draw AFTER n discarded steps
+            nxt = lib.pcu_xs_discard(state, n + 1)
+            assert int(out[0]) == nxt
+    finally:
+        oracle.orc_set_engine_kind(0)
+    assert lib.pcu_xs_discard(77, 2**40) == lib.pcu_xs_discard(lib.pcu_xs_discard(77, 2**39), 2**39)
 
 
 def test_unpack2_roundtrip():

@@ -45,7 +45,7 @@ def test_dropin_host_logic_and_concepts():
 def test_dropin_matches_reference_on_gpu():
     out = _run("--gpu")
     for part in ("single inference ok", "batch inference ok", "TreeBandit<Exp3>", "OffPolicy<Exp3>", "threaded copies ok",
-                 "batching adapter ok", "every tree == reference"):
+                 "batching adapter ok", "every tree == reference", "variants ok"):
         assert part in out
 
 

@@ -749,6 +749,82 @@ def test_words_mode_mold_and_multi(ctx, mctx, oracle):
 
 
 # ---------------------------------------------------------------------------------------------
+# Variants: Pinyon's xor_shift PRNG as the type list's PRNG, and GrowLib::alternating_constant_actions as
+# actions_func — the one-rollout-per-thread kernel k_thread.  The oracle's restatement of both is pinned to the compiled
+# reference (tests/test_oracle.py::test_variant_golden, test_variants_oracle_vs_reference).
+
+
+@pytest.mark.parametrize("shape", [(3, 3, 1, (0, 1)), (1, 3, 2, (3, 10)), (3, 1, 1, (0, 1)), (4, 5, 3, (1, 2)), (9, 9, 3, (0, 1))])
+@pytest.mark.parametrize("growth", [0, 1])
+@pytest.mark.parametrize("mode", ["S", "P"])
+def test_variant_xor_shift_tree(ctx, oracle, shape, growth, mode):
+    rows, cols, T, thr = shape
+    rng = np.random.default_rng(rows * 7 + cols + growth)
+    n = 3000
+    depth = rng.integers(1, 10, n).astype(np.uint32)
+    kw = dict(state_seed=rng.integers(1, 2**63, n).astype(np.uint64), state_pre_discard=rng.integers(0, 40, n).astype(np.uint32),
+              transition_seed=rng.integers(0, 2**63, n).astype(np.uint64), payoff_bias=rng.integers(-2, 3, n).astype(np.int32))
+    mseeds = rng.integers(1, 2**63, n).astype(np.uint64) if mode == "P" else None
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth, model_seed=987654321,
+                                      model_seeds=mseeds, engine="xs", growth=growth, **kw)
+    out = dict(payoff=np.full(n, 255, np.uint8), traj=np.zeros((n, 9, 3), np.uint8), traj_hash=np.zeros(n, np.uint32),
+               sums=np.zeros(8, np.uint64))
+    xs_state = np.array([987654321], np.uint64) if mode == "S" else None
+    ctx.rollout_random_tree(n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth.astype(np.uint16),
+                            state_seed=exp["state_after_ctor"], transition_seed=kw["transition_seed"], payoff_bias=kw["payoff_bias"],
+                            model_seeds=mseeds, xs_state=xs_state, xor_shift=True, growth=growth, traj_stride=9, **out)
+    assert ctx.last_path == "thread_tree_xs"
+    check_same(out, exp, n)
+    if mode == "S":  # the model engine ends where the reference's would: two draws per step
+        assert int(xs_state[0]) == ctx.lib.pcu_xs_discard(987654321, 2 * int(depth.sum()))
+
+
+@pytest.mark.parametrize("shape", [(3, 3, 1, (0, 1)), (1, 3, 2, (3, 10)), (3, 1, 1, (0, 1)), (4, 5, 3, (1, 2))])
+@pytest.mark.parametrize("mode", ["S", "P", "W"])
+def test_variant_growth_mt19937(ctx, oracle, shape, mode):
+    rows, cols, T, thr = shape
+    rng = np.random.default_rng(rows * 11 + cols)
+    n = 2000
+    depth = rng.integers(1, 10, n).astype(np.uint32) if mode != "S" else 7
+    kw = dict(state_seed=rng.integers(0, 2**63, n).astype(np.uint64), state_pre_discard=rng.integers(0, 700, n).astype(np.uint32),
+              transition_seed=rng.integers(0, 2**63, n).astype(np.uint64), payoff_bias=rng.integers(-2, 3, n).astype(np.int32))
+    mseeds = rng.integers(0, 2**63, n).astype(np.uint64) if mode != "S" else None
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth, model_seed=31,
+                                      model_pre_discard=5, model_seeds=mseeds, growth=1, **kw)
+    dmax = int(np.max(depth))
+    out = dict(payoff=np.full(n, 255, np.uint8), traj=np.zeros((n, dmax, 3), np.uint8), traj_hash=np.zeros(n, np.uint32),
+               sums=np.zeros(8, np.uint64))
+    gen = 2 * rows * cols * T
+    eng = Engine(31).discard(5) if mode == "S" else None
+    ctx.rollout_random_tree(n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth.astype(np.uint16) if mode != "S" else depth,
+                            state_seed=kw["state_seed"], state_pos=kw["state_pre_discard"] + np.uint32(gen),
+                            transition_seed=kw["transition_seed"], payoff_bias=kw["payoff_bias"], engine=eng,
+                            model_seeds=mseeds if mode == "P" else None,
+                            model_words=_words_for(mseeds, depth) if mode == "W" else None, growth=1, traj_stride=dmax, **out)
+    assert ctx.last_path == "thread_tree_growth"
+    check_same(out, exp, n)
+    if mode == "S":
+        assert engine_matches(eng, 31, 5 + 4 * 7 * n, oracle)
+
+
+@pytest.mark.parametrize("mode", ["S", "P"])
+def test_variant_xor_shift_mold(ctx, oracle, mode):
+    rng = np.random.default_rng(3)
+    n = 5000
+    depth = rng.integers(0, 14, n).astype(np.uint32)
+    mseeds = rng.integers(1, 2**63, n).astype(np.uint64) if mode == "P" else None
+    exp = loader.mold_rollouts(oracle, n, n_actions=3, depth=depth, model_seed=4242, model_seeds=mseeds, engine="xs")
+    traj = np.zeros((n, 13, 3), np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    xs_state = np.array([4242], np.uint64) if mode == "S" else None
+    ctx.rollout_mold(n, n_actions=3, depth=depth.astype(np.uint16), model_seeds=mseeds, xs_state=xs_state, xor_shift=True,
+                     traj=traj, traj_stride=13, traj_hash=th, sums=sums)
+    assert ctx.last_path == "thread_mold_xs"
+    assert np.array_equal(traj, exp["traj"]) and np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
+
+
+# ---------------------------------------------------------------------------------------------
 # One context over several GPUs (pcu_create_multi).  On a one-GPU box the shards share GPU 0 (listing a device twice is
 # allowed for exactly this): the shard plan, the per-shard slices of the global jump family, the output offsets and the
 # post-batch engine are the same code; only the reduction differs (a summing kernel instead of ncclAllReduce).

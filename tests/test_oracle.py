@@ -159,6 +159,52 @@ def test_oracle_vs_reference_prng(oracle, reference):
         assert np.array_equal(x.view(np.uint64), y.view(np.uint64))
 
 
+def _variant_arrays(e):
+    dt = dict(state_seed=np.uint64, state_pre_discard=np.uint32, transition_seed=np.uint64, depth=np.uint32,
+              payoff_bias=np.int32)
+    return {k: np.array(v, dtype=dt[k]) for k, v in e["arrays"].items()}
+
+
+@pytest.mark.parametrize("entry", GOLDEN.get("variants", []), ids=lambda e: f"{e['engine']}-g{e['growth']}-{e['rows']}x{e['cols']}x{e['transitions']}")
+def test_variant_golden(oracle, entry):
+    """SURVEY 8(f)4 variants: the restatement of xor_shift (random.hh:66-121) and of GrowLib::alternating_constant_actions
+    (grow-lib.hh:16-24) against vectors the compiled reference produced (make_golden.py)."""
+    e = entry
+    res = loader.random_tree_rollouts(oracle, e["n"], rows=e["rows"], cols=e["cols"], transitions=e["transitions"],
+                                      thr=tuple(e["thr"]), model_seed=e["model_seed"], model_pre_discard=e["model_pre_discard"],
+                                      engine=e["engine"], growth=e["growth"], **_variant_arrays(e))
+    assert res["payoff"].tolist() == e["payoff_x2"]
+    assert res["traj"].reshape(e["n"], -1).tolist() == e["traj"]
+    assert int(res["steps"]) == e["steps"]
+    if e["engine"] == "xs":
+        assert [int(x) for x in res["state_after_ctor"]] == e["state_after_ctor"]
+
+
+def test_variant_mold_xor_shift_golden(oracle):
+    e = GOLDEN["variants_mold_xs"]
+    res = loader.mold_rollouts(oracle, e["n"], n_actions=3, depth=np.array(e["depth"], np.uint32), model_seed=e["model_seed"],
+                               engine="xs")
+    assert res["traj"].reshape(e["n"], -1).tolist() == e["traj"]
+
+
+def test_variants_oracle_vs_reference(oracle, reference):
+    rng = np.random.default_rng(5)
+    n = 200
+    for engine, growth in (("xs", 0), ("xs", 1), ("mt", 1)):
+        for rows, cols, T, thr in ((2, 2, 1, (0, 1)), (1, 4, 3, (3, 10)), (5, 1, 2, (1, 2)), (3, 4, 8, (1, 1))):
+            kw = dict(rows=rows, cols=cols, transitions=T, thr=thr, depth=rng.integers(1, 10, n).astype(np.uint32),
+                      state_seed=rng.integers(1, 2**63, n).astype(np.uint64),
+                      state_pre_discard=rng.integers(0, 30, n).astype(np.uint32),
+                      transition_seed=rng.integers(0, 2**63, n).astype(np.uint64),
+                      payoff_bias=rng.integers(-2, 3, n).astype(np.int32), engine=engine, growth=growth)
+            for ms in (None, rng.integers(1, 2**63, n).astype(np.uint64)):
+                a = loader.random_tree_rollouts(oracle, n, model_seed=3, model_seeds=ms, **kw)
+                b = loader.random_tree_rollouts(reference, n, model_seed=3, model_seeds=ms, prefix="ref", **kw)
+                assert np.array_equal(a["payoff"], b["payoff"]) and np.array_equal(a["traj"], b["traj"])
+                if engine == "xs":
+                    assert np.array_equal(a["state_after_ctor"], b["state_after_ctor"])
+
+
 def test_golden_file_is_current(reference):
     """The committed vectors are what the reference produces today (spot check, first case)."""
     e = GOLDEN["tree"][1]
