@@ -79,7 +79,7 @@ struct pcu_ctx {
     int streams_per_sm = 0; /* model streams (generator warps) resident per SM; 0 = by batch size (run_stream) */
     double dense_streams_from = 5e7; /* rollout-steps per call from which 8 streams per SM pay for their checkpoints */
     int force_general = 0;
-    int rb = 32;        /* rollouts per consumer batch of the fused kernels (32 or 64) */
+    int rb = 0;         /* rollouts per consumer batch of the fused kernels (32, 64, 128; 0 = by output, see run_stream) */
     int small_path = 1; /* <= 32 rollouts in mode S from host memory: one k_small launch */
     bool small_attr[2] = {false, false};
     uint8_t *pin_out = nullptr; /* pinned staging for k_small's outputs (PIN_OUT_BYTES) */
@@ -669,7 +669,11 @@ int run_stream(pcu_ctx *ctx, Stream2Params &P, uint32_t rows, pcu_model_rng *rng
     P.streams = (uint32_t)((n + P.chunk - 1) / P.chunk);
     ctx->last_chunk = P.chunk;
     ctx->last_streams = P.streams;
-    P.rb = od.packed ? 128 : ctx->rb; /* the packed output is one byte per lane: four consecutive rollouts */
+    /* rollouts per consumer batch.  The packed output is one byte per lane: four consecutive rollouts (128).  Byte
+     * payoffs stored straight into pinned host memory also want 128 — a warp then writes whole 128-byte lines, i.e.
+     * full-size PCIe writes (8 GPUs, r2i: e2e 7.1e10 -> 8.8e10 rollouts/s) — while payoffs that stay in HBM are
+     * fastest at 32 (1.181e11 against 1.147e11). */
+    P.rb = od.packed ? 128 : (ctx->rb ? ctx->rb : (od.payoff_direct ? 128 : 32));
     if (!stream_fits(P.depth, (uint64_t)rows * P.cols, P.rb)) P.rb = 32;
     P.bcodes = P.rb * P.depth;
     P.ring_codes = stream_ring_codes(P.rb, P.depth);
@@ -1214,7 +1218,7 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
         return PCU_OK;
     }
     if (!strcmp(key, "rb")) {
-        if (value != 32 && value != 64 && value != 128) return PCU_ERR_INVALID;
+        if (value != 0 && value != 32 && value != 64 && value != 128) return PCU_ERR_INVALID;
         ctx->rb = (int)value;
         return PCU_OK;
     }

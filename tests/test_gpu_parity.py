@@ -483,7 +483,7 @@ def test_stream_geometry_matrix(ctx, oracle, case, per_sm, rb):
             assert engine_matches(eng, mseed, mpre + 4 * depth * n, oracle)
     finally:
         ctx.set_option("streams_per_sm", 0)
-        ctx.set_option("rb", 32)
+        ctx.set_option("rb", 0)
 
 
 @pytest.mark.parametrize("per_sm", [1, 8, 16])
@@ -501,7 +501,7 @@ def test_mold_geometry_matrix(ctx, oracle, per_sm, rb):
         assert ctx.last_path == "stream_mold"
     finally:
         ctx.set_option("streams_per_sm", 0)
-        ctx.set_option("rb", 32)
+        ctx.set_option("rb", 0)
     assert np.array_equal(th, exp["traj_hash"]) and np.array_equal(sums, exp["sums"])
     assert engine_matches(eng, 3, 4 * depth * n, oracle)
 
