@@ -231,6 +231,24 @@ typedef struct {
 int pcu_rollout_random_tree(pcu_ctx *ctx, const pcu_rt_batch *batch, pcu_model_rng *rng, pcu_out *out);
 int pcu_rollout_mold(pcu_ctx *ctx, const pcu_mold_batch *batch, pcu_model_rng *rng, pcu_out *out);
 
+/* NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * A leaf batch of ONE RandomTree state in model-rng mode W (what pcu_rollout_random_tree does with rng->mode ==
+ * PCU_MODEL_WORDS, batch->mem == PCU_MEM_DEVICE and batch-uniform fields: path "leaf_table_W") that allocates no device
+ * memory: the state-stream table, that path's only scratch, lives in a static device array of
+ * PCU_NOALLOC_SCRATCH_BYTES that every GPU which loads the library holds until the process exits.
+ *   batch        every per-rollout pointer NULL (the *_u scalars describe the one state), growth default, mem ignored
+ *   d_words      DEVICE u32[n * 4 * depth_u]: each leaf's raw engine words (pcu_mt_take_raw), leaf-major
+ *   d_payoff_x2  DEVICE u8[n], may be NULL;  d_sums  DEVICE u64[8] as pcu_out.sums, may be NULL (cleared by the call)
+ * Limits, rejected with PCU_ERR_INVALID and a message in pcu_last_error: n <= PCU_NOALLOC_MAX_LEAVES, and the table
+ * ((2*R*C*T + (3*R*C*T + 2) * depth + 8) bytes, twice that when T > 1) must fit the scratch; single-GPU contexts only.
+ * Calls no cudaMalloc / cudaFree; runs on the context's stream and returns when the outputs are complete.  All calls
+ * on a device share the array, which keeps the last call's table: calls that overlap on one GPU race. */
+#define PCU_NOALLOC_SCRATCH_BYTES (64u * 1024u)
+#define PCU_NOALLOC_MAX_LEAVES (1ull << 24)
+int pcu_leaf_batch_noalloc(pcu_ctx *ctx, const pcu_rt_batch *batch, const uint32_t *d_words, uint8_t *d_payoff_x2,
+                           uint64_t *d_sums);
+
 /* Name of the kernel path the last rollout call took ("stream_table", "stream_mold",
  * "warp_private", ...); for tests and benchmarks. */
 const char *pcu_last_path(const pcu_ctx *ctx);

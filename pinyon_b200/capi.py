@@ -45,6 +45,7 @@ EXPORTS = [
     "pcu_set_option", "pcu_host_alloc", "pcu_host_free", "pcu_mt_seed", "pcu_mt_discard", "pcu_mt_next", "pcu_mt_discard_family",
     "pcu_rollout_random_tree", "pcu_rollout_mold", "pcu_last_path", "pcu_measure_int_peak",
     "pcu_create_multi", "pcu_device_count", "pcu_get_stat", "pcu_warmup", "pcu_visible_devices", "pcu_mt_take_raw", "pcu_xs_discard",
+    "pcu_leaf_batch_noalloc",
 ]
 
 
@@ -133,6 +134,8 @@ def load_library(build_if_missing: bool = True) -> C.CDLL:
     lib.pcu_visible_devices.restype = C.c_int
     lib.pcu_get_stat.argtypes = [vp, C.c_char_p, C.POINTER(C.c_double)]
     lib.pcu_warmup.argtypes = [vp, u64, u32]
+    lib.pcu_leaf_batch_noalloc.argtypes = [vp, C.POINTER(RtBatch), vp, vp, vp]
+    lib.pcu_leaf_batch_noalloc.restype = C.c_int
     _lib = lib
     return lib
 
@@ -350,6 +353,20 @@ class Context:
         r = self._rng(engine, model_seeds, model_words, xs_state, xor_shift)
         o = self._out(device, payoff, traj, traj_stride, traj_hash, sums, payoff_packed)
         self._check(self.lib.pcu_rollout_random_tree(self.h, C.byref(b), C.byref(r), C.byref(o)))
+
+    def leaf_batch_noalloc(self, n, *, rows, cols, transitions=1, thr=(0, 1), depth, state_seed=0, state_pos=None,
+                           transition_seed=0, payoff_bias=0, words, payoff=None, sums=None):
+        """pcu_leaf_batch_noalloc: leaves of ONE state, mode W, no device allocation inside the library.  `words`,
+        `payoff`, `sums` are torch CUDA tensors (uint32-as-int32 / uint8 / int64 storage) owned by the caller."""
+        b = RtBatch()
+        b.n = n
+        b.state_seed_u, b.transition_seed_u = int(state_seed), int(transition_seed)
+        b.state_pos_u = 2 * rows * cols * transitions if state_pos is None else int(state_pos)
+        b.depth_u, b.payoff_bias_u = int(depth), int(payoff_bias)
+        b.rows, b.cols, b.transitions = rows, cols, transitions
+        b.thr_p, b.thr_q = thr
+        b.mem = PCU_MEM_DEVICE
+        self._check(self.lib.pcu_leaf_batch_noalloc(self.h, C.byref(b), _ptr(words), _ptr(payoff), _ptr(sums)))
 
     def rollout_mold(self, n, *, n_actions, depth, engine: Engine = None, model_seeds=None, payoff=None, traj=None,
                      traj_stride=0, traj_hash=None, sums=None, payoff_packed=None, model_words=None, xs_state=None,

@@ -2414,3 +2414,102 @@ int pcu_measure_int_peak(pcu_ctx *ctx, int variant, int reps, double *ops_per_se
 }
 
 }  // extern "C"
+
+/* ---- pcu_leaf_batch_noalloc: a leaf batch with the state-stream table in STATIC device memory ---------------------
+ * No counterpart in the reference; added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  It is the "leaf_table_W" path (k_leaf_table,
+ * leaf.cuh) with its one piece of device scratch, the state-stream table, in the file-scope array below instead of a
+ * grown-on-demand context buffer.  Every GPU that loads the library holds the array until the process exits.  All calls
+ * on a device share it and it keeps the last call's table: each call rewrites the whole range it reads (nothing has to
+ * start at zero; the caller's sums are cleared here), and calls that overlap on one GPU race. */
+static __device__ __align__(256) uint8_t g_noalloc_scratch[PCU_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+uint8_t *g_noalloc_dev_ptr[NOALLOC_MAX_DEVICES]; /* DEVICE address of g_noalloc_scratch per device (the name itself is
+                                                    a host-side stand-in in host code, not a device address) */
+
+/* once per device, with that device current */
+int noalloc_scratch(pcu_ctx *ctx, uint8_t **out) {
+    if (ctx->device < 0 || ctx->device >= NOALLOC_MAX_DEVICES)
+        return fail(ctx, PCU_ERR_INVALID, "pcu_leaf_batch_noalloc: device index %d out of range", ctx->device);
+    std::lock_guard<std::mutex> lock(g_noalloc_mu);
+    if (!g_noalloc_dev_ptr[ctx->device]) {
+        CU(cudaSetDevice(ctx->device));
+        uint8_t *p = nullptr;
+        CU(cudaGetSymbolAddress((void **)&p, g_noalloc_scratch));
+        if (!p) return fail(ctx, PCU_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_noalloc_dev_ptr[ctx->device] = p;
+    }
+    *out = g_noalloc_dev_ptr[ctx->device];
+    return PCU_OK;
+}
+}  // namespace
+
+extern "C" int pcu_leaf_batch_noalloc(pcu_ctx *ctx, const pcu_rt_batch *b, const uint32_t *d_words, uint8_t *d_payoff_x2,
+                                      uint64_t *d_sums) {
+    if (!ctx) return PCU_ERR_INVALID;
+    if (ctx->multi) return fail(ctx, PCU_ERR_INVALID, "pcu_leaf_batch_noalloc needs a single-GPU context (pcu_create)");
+    if (!b || !d_words || (!d_payoff_x2 && !d_sums))
+        return fail(ctx, PCU_ERR_INVALID, "pcu_leaf_batch_noalloc: null batch, words or outputs");
+    if (b->state_seed || b->state_pos || b->transition_seed || b->depth || b->payoff_bias)
+        return fail(ctx, PCU_ERR_INVALID, "pcu_leaf_batch_noalloc takes batch-uniform fields only (leaves of ONE state)");
+    if (b->growth != PCU_GROWTH_DEFAULT) return fail(ctx, PCU_ERR_UNSUPPORTED, "pcu_leaf_batch_noalloc: default growth only");
+    const uint32_t T = b->transitions;
+    if (b->rows < 1 || b->rows > 255 || b->cols < 1 || b->cols > 255 || T < 1 || b->depth_u < 1 || b->thr_q < 1)
+        return fail(ctx, PCU_ERR_INVALID, "pcu_leaf_batch_noalloc: rows, cols in 1..255, transitions, depth, thr_q >= 1");
+    if (T > 8) return fail(ctx, PCU_ERR_UNSUPPORTED, "transitions > 8");
+    if (b->n == 0) return PCU_OK;
+    if (b->n > PCU_NOALLOC_MAX_LEAVES)
+        return fail(ctx, PCU_ERR_INVALID, "pcu_leaf_batch_noalloc: %llu leaves exceed the maximum of %llu",
+                    (unsigned long long)b->n, (unsigned long long)PCU_NOALLOC_MAX_LEAVES);
+    const uint32_t gen_words = 2u * b->rows * b->cols * T;
+    if (b->state_pos_u < gen_words)
+        return fail(ctx, PCU_ERR_INVALID, "state_pos is below 2*rows*cols*transitions");
+    const uint64_t per_step = (uint64_t)b->rows * b->cols * T + 2 + gen_words;
+    const uint64_t span = (uint64_t)gen_words + per_step * b->depth_u + 8;
+    const uint64_t bytes = span * (T > 1 ? 2 : 1);
+    if (bytes > PCU_NOALLOC_SCRATCH_BYTES)
+        return fail(ctx, PCU_ERR_INVALID,
+                    "pcu_leaf_batch_noalloc: the state-stream table of this shape and depth needs %llu bytes, the static "
+                    "scratch holds %llu (use pcu_rollout_random_tree)",
+                    (unsigned long long)bytes, (unsigned long long)PCU_NOALLOC_SCRATCH_BYTES);
+    uint8_t *scratch = nullptr;
+    int rc;
+    if ((rc = noalloc_scratch(ctx, &scratch))) return rc;
+    CU(cudaSetDevice(ctx->device));
+
+    const uint32_t tab_base = b->state_pos_u - gen_words, tab_len = (uint32_t)span;
+    const double pu = (T > 1) ? host_uniform_from_seed(b->transition_seed_u) : 0.0;
+    std::vector<uint8_t> tab; /* host heap only */
+    host_build_table(b->state_seed_u, tab_base, tab_len, T, pu, b->thr_p, b->thr_q, tab);
+    if (tab.size() != bytes) return fail(ctx, PCU_ERR_INVALID, "internal: table size mismatch");
+    CU(cudaMemcpyAsync(scratch, tab.data(), tab.size(), cudaMemcpyHostToDevice, ctx->stream));
+    if (d_sums) CU(cudaMemsetAsync(d_sums, 0, sizeof(uint64_t) * 8, ctx->stream));
+
+    LeafParams L;
+    memset(&L, 0, sizeof(L));
+    L.n = b->n;
+    L.kind = KIND_TREE;
+    L.cols = b->cols;
+    L.T = T;
+    L.gen_words = gen_words;
+    L.mrow = make_fold_const(b->rows);
+    L.mcol = make_fold_const(b->cols);
+    L.words = d_words;
+    L.depth_u = b->depth_u;
+    L.tab = scratch;
+    L.tab_base = tab_base;
+    L.tab_len = tab_len;
+    L.state_pos_u = b->state_pos_u;
+    L.bias_u = b->payoff_bias_u;
+    L.payoff = d_payoff_x2;
+    L.sums = reinterpret_cast<unsigned long long *>(d_sums);
+    k_leaf_table<<<(unsigned)((L.n + 127) / 128), 128, 0, ctx->stream>>>(L);
+    ctx->launches++;
+    CU(cudaGetLastError());
+    CU(cudaStreamSynchronize(ctx->stream)); /* the host table must outlive the copy; outputs are complete on return */
+    ctx->path = "leaf_table_noalloc";
+    return PCU_OK;
+}
