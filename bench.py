@@ -42,12 +42,12 @@ WORKLOADS = {
     # chain 397*3 + lock-step 227*(3+3+5) + tail 56*(3+5) + play 10*45.
     "tree_d10_3x3x1_dr": dict(kind="tree", rows=3, cols=3, T=1, depth=10, log2n=24, ops_step=318.0, ops_setup=2492.0,
                               ops_exec=458.6, dr=True, kernel="k_lane_pre + k_lane<TREE,S>"),
-    # config B with distinct roots and distinct transition seeds -> k_seed_pre + k_warp (private
-    # 624-word engines refilled ~19.5 times per rollout).  2^20 rollouts per GPU (the CPU needs ~0.3 ms per rollout).
-    # ops_setup = 2492 (state seeding) + 1592 (transition prng); ops_exec per rollout = 430 warp instructions per step
-    # of which 55 % are int32 ALU/FMA-pipe instructions (ncu r1e, r1g) x 32 lanes = 7150 int ops per step.
+    # config B with distinct roots and distinct transition seeds -> k_warp2 (private 624-word engines
+    # seeded and advanced in shared memory, ~20 refills per rollout).  2^20 rollouts per GPU (the CPU needs ~0.3 ms per
+    # rollout).  ops_setup = 2492 (state seeding) + 1592 (transition prng); ops_exec per rollout = 427 warp instructions
+    # per step of which 51 % are int32 ALU/FMA-pipe instructions (ncu r2u) x 32 lanes = 6980 int ops per step.
     "tree_d20_9x9x3_dr": dict(kind="tree", rows=9, cols=9, T=3, depth=20, log2n=20, ops_step=4920.0, ops_setup=4084.0,
-                              ops_exec=7150.0, dr=True, kernel="k_seed_pre + k_warp<TREE,S>"),
+                              ops_exec=6980.0, dr=True, kernel="k_warp2<1> (seeders + players)"),
     "mold_2_10": dict(kind="mold", rows=2, cols=2, T=1, depth=10, log2n=24, ops_step=104.0, ops_exec=70.0,
                       kernel="k_stream2<MOLD,u8>"),
 }
@@ -473,7 +473,7 @@ def roofline(w, m, int_peak, int_peak_alu, peaks, peak_kind, workload_name):
     if w.get("dr"):
         note += ("DISTINCT-ROOT run: every rollout seeds and advances its own state engine (+%.0f ops per rollout "
                  "for the seeding chains, included in achieved); `executed` counts the %.0f ops per rollout the "
-                 "kernels really issue. kernel_ms brackets the seeding pre-kernel + the rollout kernel (%s); the "
+                 "kernels really issue. kernel_ms brackets the seeding and the rollouts (%s); the "
                  "model-stream code generator (k_gen_codes2 + jump-ahead) runs before it and is in ms_per_step only"
                  % (w["ops_setup"], w["ops_exec"] * depth, w["kernel"]))
     else:

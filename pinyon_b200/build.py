@@ -16,7 +16,7 @@ ROOT = PKG.parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libpinyon_cuda.so"
 SOURCES = [CSRC / "pinyon_cuda.cu", CSRC / "mt_jump.cu", CSRC / "mt_poly.cpp"]
-HEADERS = [CSRC / "kernels.cuh", CSRC / "stream.cuh", CSRC / "lane.cuh", CSRC / "seed.cuh", CSRC / "leaf.cuh", CSRC / "thread.cuh", CSRC / "mt19937.cuh", CSRC / "mt_jump.h", ROOT / "include" / "pinyon_cuda.h"]
+HEADERS = [CSRC / "kernels.cuh", CSRC / "stream.cuh", CSRC / "lane.cuh", CSRC / "seed.cuh", CSRC / "leaf.cuh", CSRC / "thread.cuh", CSRC / "warp2.cuh", CSRC / "mt19937.cuh", CSRC / "mt_jump.h", ROOT / "include" / "pinyon_cuda.h"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

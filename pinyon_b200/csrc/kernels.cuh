@@ -418,6 +418,7 @@ __global__ void __launch_bounds__(1024) k_small(const __grid_constant__ SmallPar
 #include "seed.cuh"
 #include "leaf.cuh"
 #include "thread.cuh"
+#include "warp2.cuh"
 
 /* ------------------------------------------------------- integer-issue peak probe */
 

@@ -86,6 +86,8 @@ struct pcu_ctx {
     int zero_copy = 1; /* payoffs of large batches go straight to pinned host buffers */
     int lane_full_columns = 0; /* test hook: k_lane keeps every row (no ring) */
     int force_warp = 0; /* test hook: keep distinct-root batches on k_warp instead of k_lane */
+    int warp2_lock = 1; /* rollouts a k_warp2 player warp steps in lock-step: 1, 2 or 4 */
+    int warp2 = 1;      /* test hook: 0 keeps modes S/W of the general path on k_seed_pre + k_warp instead of k_warp2 */
     int host_checkpoints = 0; /* test hook: brute-force checkpoints on the host instead of the jump kernels */
     DevBuf buf[B_COUNT];
     uint32_t *pin_small = nullptr; /* pinned staging: engine window out */
@@ -885,6 +887,37 @@ int launch_warp(pcu_ctx *ctx, const WarpParams &P0) {
     return PCU_OK;
 }
 
+/* k_warp2 (warp2.cuh): one persistent CTA per SM, the private engines seeded and played in shared memory. */
+template <int LOCK>
+int launch_warp2_lock(pcu_ctx *ctx, const Warp2Params &P, size_t smem, unsigned blocks) {
+    auto kern = k_warp2<LOCK>;
+    CU(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    CU(cudaEventRecord(ctx->ev0, ctx->stream));
+    kern<<<blocks, W2Cfg<LOCK>::THREADS, smem, ctx->stream>>>(P);
+    ctx->launches++;
+    CU(cudaEventRecord(ctx->ev1, ctx->stream));
+    ctx->ev_valid = true;
+    CU(cudaGetLastError());
+    return PCU_OK;
+}
+
+int launch_warp2(pcu_ctx *ctx, const WarpParams &W0) {
+    Warp2Params P;
+    memset(&P, 0, sizeof(P));
+    P.w = W0;
+    P.w.i0 = 0;
+    P.w.i1 = W0.n;
+    P.pu_u = (W0.T > 1 && !W0.tseed) ? host_uniform_from_seed(W0.tseed_u) : 0.0;
+    P.mulc = 1812433253u;
+    const size_t smem = sizeof(uint32_t) * W2_SLOTS * W2_STRIDE + sizeof(double) * 11 * (W0.T > 1 ? W0.fq_w : 0) + sizeof(W2Ctl);
+    const unsigned blocks = (unsigned)std::max<uint64_t>(1, std::min<uint64_t>((W0.n + 31) / 32, (uint64_t)ctx->sms));
+    switch (ctx->warp2_lock) {
+        case 1: return launch_warp2_lock<1>(ctx, P, smem, blocks);
+        case 2: return launch_warp2_lock<2>(ctx, P, smem, blocks);
+        default: return launch_warp2_lock<4>(ctx, P, smem, blocks);
+    }
+}
+
 /* Draw-index bound and largest depth of a batch (k_lane's shared-memory column height).
  * Batch-uniform positions and depths need no kernel. */
 int lane_bound(pcu_ctx *ctx, uint64_t n, const uint32_t *d_pos, uint32_t pos_u, const uint16_t *d_depth,
@@ -1228,6 +1261,15 @@ int pcu_set_option(pcu_ctx *ctx, const char *key, int64_t value) {
     }
     if (!strcmp(key, "zero_copy")) {
         ctx->zero_copy = value != 0;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "warp2_lock")) {
+        if (value != 1 && value != 2 && value != 4) return fail(ctx, PCU_ERR_INVALID, "warp2_lock is 1, 2 or 4");
+        ctx->warp2_lock = (int)value;
+        return PCU_OK;
+    }
+    if (!strcmp(key, "warp2")) {
+        ctx->warp2 = value != 0;
         return PCU_OK;
     }
     if (!strcmp(key, "force_warp")) {
@@ -1798,7 +1840,8 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
     uint64_t lane_words = 0, lane_dmax = 0;
     LaneGeom geom;
     bool lane = !ctx->force_warp && T == 1;
-    if (lane || d_pos) { /* per-rollout positions are range-checked on every path (k_warp would index its engine below 0) */
+    bool warp2 = ctx->warp2 && rng->mode != PCU_MODEL_PER_ROLLOUT;
+    if (lane || d_pos || warp2) { /* per-rollout positions are range-checked on every path (k_warp would index its engine below 0) */
         const uint32_t per_step = gen_words + b->rows * b->cols * T - 1 + 2;
         if ((rc = lane_bound(ctx, n, d_pos, b->state_pos_u, d_depth, b->depth_u, gen_words, per_step, &lane_words,
                              &lane_dmax, &geom.pos_min, &geom.pos_max)))
@@ -1807,11 +1850,12 @@ int rollout_tree(pcu_ctx *ctx, const pcu_rt_batch *b, pcu_model_rng *rng, pcu_ou
         lane = lane && lane_words <= MT_N - 1 && (rng->mode != PCU_MODEL_PER_ROLLOUT || 4 * lane_dmax <= MT_LAG - 3);
         geom.words = (uint32_t)lane_words;
         geom.dmax = (uint32_t)lane_dmax;
+        warp2 = warp2 && lane_words + 16 < (1ull << 31); /* k_warp2 keeps 32-bit draw indices */
     }
     if (rng->mode != PCU_MODEL_PER_ROLLOUT) { /* modes S and W: the kernels take joint action codes */
         const bool w = rng->mode == PCU_MODEL_WORDS;
         ctx->path = lane ? (w ? "lane_private_W" : "lane_private_S") : (w ? "warp_private_W" : "warp_private_S");
-        rc = lane ? launch_lane<KIND_TREE, 0>(ctx, W, geom) : launch_warp<KIND_TREE, 0>(ctx, W);
+        rc = lane ? launch_lane<KIND_TREE, 0>(ctx, W, geom) : warp2 ? launch_warp2(ctx, W) : launch_warp<KIND_TREE, 0>(ctx, W);
     } else {
         ctx->path = lane ? "lane_private_P" : "warp_private_P";
         rc = lane ? launch_lane<KIND_TREE, 1>(ctx, W, geom) : launch_warp<KIND_TREE, 1>(ctx, W);

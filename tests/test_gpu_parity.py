@@ -221,6 +221,45 @@ def test_tree_lane_boundary(ctx, oracle, extra, path):
     check_same(got, exp, n)
 
 
+@pytest.mark.parametrize("case", [
+    dict(rows=9, cols=9, T=3, thr=(0, 1), n=148 * 96 + 77, dmax=20),   # config 3 with distinct roots: every ring reused
+    dict(rows=4, cols=3, T=2, thr=(3, 10), n=5000, dmax=40),            # thresholds; depth > 32: two code fetches
+    dict(rows=3, cols=3, T=1, thr=(0, 1), n=3000, dmax=70),             # one transition, draws far past the first refill
+    dict(rows=2, cols=2, T=8, thr=(1, 1), n=45, dmax=9),                # a partial second seeder pass
+])
+def test_warp2_against_oracle_and_k_warp(ctx, oracle, case):
+    """k_warp2 (engines seeded and played in shared memory) against the oracle and against k_seed_pre + k_warp
+    (option warp2 = 0) on ragged depths, per-rollout positions, biases, state and transition seeds."""
+    rows, cols, T, thr, n, dmax = (case[k] for k in ("rows", "cols", "T", "thr", "n", "dmax"))
+    rng = np.random.default_rng(n + T)
+    depth = rng.integers(1, dmax + 1, n).astype(np.uint32)
+    depth[:3] = dmax
+    pre = rng.integers(0, 3000, n).astype(np.uint32)
+    bias = rng.integers(-2, 3, n).astype(np.int32)
+    seeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    tseeds = rng.integers(0, 2**63, n).astype(np.uint64)
+    exp = loader.random_tree_rollouts(oracle, n, rows=rows, cols=cols, transitions=T, thr=thr, depth=depth, model_seed=6,
+                                      state_seed=seeds, state_pre_discard=pre, transition_seed=tseeds, payoff_bias=bias)
+    results = []
+    for warp2, lock in ((1, 4), (1, 2), (1, 1), (0, 4)):  # lock: rollouts a player warp steps in lock-step
+        ctx.set_option("warp2", warp2)
+        ctx.set_option("warp2_lock", lock)
+        ctx.set_option("force_warp", 1)
+        try:
+            eng = Engine(6)
+            got = run_tree(ctx, n, rows=rows, cols=cols, T=T, thr=thr, depth=depth, state_seed=seeds, pre=pre, tseed=tseeds,
+                           bias=bias, engine=eng)
+        finally:
+            ctx.set_option("warp2", 1)
+            ctx.set_option("warp2_lock", 1)
+            ctx.set_option("force_warp", 0)
+        assert ctx.last_path == "warp_private_S"
+        check_same(got, exp, n)
+        assert engine_matches(eng, 6, 4 * int(depth.sum()), oracle)
+        results.append(got)
+    assert all(np.array_equal(results[0]["traj"], r["traj"]) for r in results[1:])
+
+
 def test_tree_general_path_equals_fused(ctx, oracle):
     """force_general routes a shared-root batch through the warp kernel: same answers."""
     n = 600
