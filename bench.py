@@ -574,6 +574,19 @@ def run_ours(args, w, workload_name):
             if rank == 0:
                 ref = run_search_binary("ref", 0, 0, 4096, 5, 1)
                 search["reference_single_thread_leaves_per_s"] = ref["leaves_per_s"]
+            # the same search root-parallel on this rank's share of the host threads, all over this rank's GPU
+            cores = max(1, (os.cpu_count() or 1) // world)
+            rig.barrier()
+            mt = run_search_binary("gpu_op_mt", rig.local, 1000 * rank, 4096, 6, 1, cores)
+            sec = rig.reduce([mt["seconds"]], "max")[0]
+            search["root_parallel"] = {"value": 4096 * 6 * cores * world / sec, "unit": "leaves/s",
+                                       "host_threads_per_gpu": cores, "trees_per_gpu": cores,
+                                       "config": "one unmodified OffPolicy search per host thread, 4096 leaves per "
+                                                 "batched inference, the threads of a rank share its GPU context"}
+            if rank == 0:
+                refm = run_search_binary("ref_op_mt", 0, 0, 4096, 3, 1, os.cpu_count() or 1)
+                search["root_parallel"]["reference_all_threads_leaves_per_s"] = refm["leaves_per_s"]
+                search["root_parallel"]["reference_threads"] = refm["threads"]
         except Exception as exc:  # the search line is extra evidence; the headline must still print
             search = {"error": str(exc)[:300]}
     batched = None

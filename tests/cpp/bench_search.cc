@@ -8,6 +8,7 @@
 //   (ref_tb / gpu_tb: TreeBandit<Exp3>, one leaf per iteration; leaves_per_batch is ignored)
 //   bench_search gpu_tb_batched <gpu_id|-1> <seed> <leaves_per_batch> <iterations_per_tree> 0 <threads> <fibers_per_thread>
 //   bench_search ref_tb_mt 0 <seed> 0 <iterations_per_tree> 0 <threads> <trees_per_thread>
+//   bench_search <gpu_op_mt|ref_op_mt> <gpu_id> <seed> <leaves_per_batch> <learner_iterations> <warmup> <threads>
 //
 // Prints one JSON object: leaves/s over the timed learner iterations and the root statistics
 // (exp3.hh:9-16) so that the caller can check ref == gpu for equal seeds and iteration counts, and
@@ -17,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <stdexcept>
 #include <string>
 #include <thread>
 #include <vector>
@@ -163,6 +165,58 @@ static int run_tb_ref_mt(uint64_t seed, size_t iters, size_t threads, size_t tre
     return 0;
 }
 
+// Root-parallel OffPolicy: `threads` host threads, each running the reference's unmodified
+// OffPolicy<Exp3<...>> on its own tree (device prng{seed + t}, model prng{0}) with `leaves` actor iterations per batched
+// inference; the GPU models share one context (calls serialise on its mutex: 0.06 us of GPU per leaf against ~10 us of
+// host tree walk).  The same loop over the reference model is the CPU side of the comparison.
+template <typename Types, typename MakeModel>
+static int run_mt(const char *impl, uint64_t device_seed, size_t leaves, size_t iters, size_t warmup, size_t threads,
+                  MakeModel make) {
+    std::vector<long long> visits(threads, 0);
+    std::vector<double> values(threads, 0.0);
+    std::vector<std::string> errors(threads);
+    std::vector<std::unique_ptr<typename Types::Model>> models;
+    for (size_t t = 0; t < threads; ++t) models.push_back(std::make_unique<typename Types::Model>(make()));
+    std::vector<std::vector<typename Types::MatrixNode>> roots; /* MatrixNode is neither copyable nor movable */
+    roots.reserve(threads);
+    for (size_t t = 0; t < threads; ++t) roots.emplace_back(1);
+    auto body = [&](size_t t, size_t n_iter) {
+        try {
+            typename Types::PRNG device{device_seed + t};
+            std::vector<typename Types::State> states;
+            states.emplace_back(prng{0}, 10, 3, 3, 1);
+            typename Types::Search search{};
+            search.run_for_iterations(n_iter, leaves, device, states, *models[t], roots[t]);
+        } catch (const std::exception &e) {
+            errors[t] = e.what();
+        }
+    };
+    auto sweep = [&](size_t n_iter) {
+        std::vector<std::thread> pool;
+        for (size_t t = 0; t < threads; ++t) pool.emplace_back(body, t, n_iter);
+        for (auto &th : pool) th.join();
+    };
+    if (warmup) sweep(warmup);
+    const auto t0 = std::chrono::steady_clock::now();
+    sweep(iters);
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    for (auto &e : errors)
+        if (!e.empty()) throw std::runtime_error(e);
+    long long v = 0;
+    double val = 0;
+    size_t nodes = 0;
+    for (size_t t = 0; t < threads; ++t) {
+        v += roots[t][0].stats.visits;
+        val += double(roots[t][0].stats.value_total.get_row_value());
+        nodes += roots[t][0].count_matrix_nodes();
+    }
+    std::printf("{\"impl\": \"%s\", \"threads\": %zu, \"leaves_per_batch\": %zu, \"learner_iterations\": %zu, "
+                "\"warmup_iterations\": %zu, \"seconds\": %.6f, \"leaves_per_s\": %.3f, \"nodes\": %zu, \"visits\": %lld, "
+                "\"value_total_row\": %.6f}\n",
+                impl, threads, leaves, iters, warmup, sec, double(threads) * double(leaves) * double(iters) / sec, nodes, v, val);
+    return 0;
+}
+
 int main(int argc, char **argv) {
     if (argc < 7) {
         std::fprintf(stderr, "usage: %s <ref|gpu> <gpu_id> <device_seed> <leaves> <iterations> <warmup>\n", argv[0]);
@@ -178,6 +232,13 @@ int main(int argc, char **argv) {
     try {
         if (!std::strcmp(argv[1], "gpu_tb_batched")) return run_tb_batched(gpu_id, seed, leaves, iters, threads, fibers);
         if (!std::strcmp(argv[1], "ref_tb_mt")) return run_tb_ref_mt(seed, iters, threads, fibers);
+        if (!std::strcmp(argv[1], "gpu_op_mt"))
+            return run_mt<OffPolicy<Exp3<GpuTree>>>("gpu_op_mt", seed, leaves, iters, warmup, threads, [&] {
+                return GpuTree::Model{prng{0}, PinyonCuda::Device::shared(gpu_id)};
+            });
+        if (!std::strcmp(argv[1], "ref_op_mt"))
+            return run_mt<OffPolicy<Exp3<RefTree>>>("ref_op_mt", seed, leaves, iters, warmup, threads,
+                                                     [] { return RefTree::Model{prng{0}}; });
         if (!std::strcmp(argv[1], "gpu_tb"))
             return run_tb<TreeBandit<Exp3<GpuTree>>>("gpu_tb", seed, iters, warmup, [&] {
                 return GpuTree::Model{prng{0}, PinyonCuda::Device::shared(gpu_id)};

@@ -17,6 +17,11 @@ for path in sys.argv[1:]:
                 wl.get("kernel_ms", 0.0) or 0.0, (wl.get("roofline") or {}).get("executed", {}).get("frac", 0.0)))
         else:
             print("    %-28s %s" % (name, wl))
+        if "root_parallel" in wl:
+            rp = wl["root_parallel"]
+            print("    %-28s %.4g leaves/s on %s threads per GPU (reference on %s threads: %.4g)" % (
+                name + " root-parallel", rp["value"], rp.get("host_threads_per_gpu"), rp.get("reference_threads"),
+                rp.get("reference_all_threads_leaves_per_s", 0.0)))
     if "single_process_multi_gpu" in d:
         print("    single process:", d["single_process_multi_gpu"])
     if "cold_call" in d:
