@@ -575,11 +575,11 @@ static void test_multi_gpu_batch(size_t n) {
     CHECK(one.device.uniform_64() == many.device.uniform_64());
     // and the head of the batch against the reference model itself
     RefTree::Model ref{prng{3}};
-    for (int i = 0; i < 3000; ++i) {
+    for (size_t i = 0; i < std::min<size_t>(3000, n); ++i) {
         RefTree::ModelOutput a;
         GpuTree::ModelOutput b;
         ref.inference(RandomTree<>::State{root}, a);
-        many.get_output(b, out_many, i);
+        many.get_output(b, out_many, (long)i);
         CHECK(same_value(a.value, b.value));
     }
     std::printf("multi-GPU batch ok: %zu leaves over %zu shards (%d visible GPUs), path %s\n", n, ids.size(), visible,
