@@ -446,6 +446,33 @@ def test_distinct_roots_full_size_windows(ctx, oracle):
     assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
 
 
+def test_distinct_roots_config3_full_size_windows(ctx, oracle):
+    """SURVEY 8(d) M2-DR at the bench's size (2^20 rollouts of config 3, state_seed_i = i, transition_seed_i = i * phi):
+    k_warp2 with every ring reused ~90 times per CTA; exact counts and sampled windows against the oracle."""
+    n = 1 << 20
+    seeds = np.arange(n, dtype=np.uint64)
+    tseeds = seeds * np.uint64(0x9E3779B97F4A7C15)
+    payoff = np.zeros(n, np.uint8)
+    th = np.zeros(n, np.uint32)
+    sums = np.zeros(8, np.uint64)
+    eng = Engine(0)
+    ctx.rollout_random_tree(n, rows=9, cols=9, transitions=3, depth=20, state_seed=seeds, transition_seed=tseeds, engine=eng,
+                            payoff=payoff, traj_hash=th, sums=sums)
+    assert ctx.last_path == "warp_private_S"
+    assert int(sums[:3].sum()) == n and int(sums[3]) == 20 * n
+    assert np.bincount(payoff, minlength=3).tolist() == [int(sums[2]), int(sums[1]), int(sums[0])]
+    assert int(th.astype(np.uint64).sum()) == int(sums[4])
+    per_cta = -(-n // 148)  # k_warp2 gives each CTA a contiguous share: sample across a share boundary too
+    for start in (0, per_cta - 256, 543_210, n - 512):
+        exp = loader.random_tree_rollouts(oracle, 512, rows=9, cols=9, transitions=3, depth=20, model_pre_discard=80 * start,
+                                          state_seed=seeds[start:start + 512].copy(),
+                                          transition_seed=tseeds[start:start + 512].copy(), want_traj=False)
+        assert np.array_equal(payoff[start:start + 512], exp["payoff"])
+        assert np.array_equal(th[start:start + 512], exp["traj_hash"])
+    ref = Engine(0).discard(80 * n)
+    assert [eng.next() for _ in range(700)] == [ref.next() for _ in range(700)]
+
+
 @pytest.mark.parametrize("shape", [
     (255, 255, 1, (0, 1), 3),    # largest action sets: joint codes need 16 bits, one step is 195 076 state draws
     (2, 2, 8, (0, 1), 12),       # most chance transitions before the reference's Rational<int> sum overflows int
