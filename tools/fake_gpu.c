@@ -1,5 +1,9 @@
-/* Profiling shim (NOT part of the product or the tests): a fake libpinyon_cuda front for the host-side batching
- * adapter, so that its overhead can be measured on a machine without a GPU.  LD_PRELOAD it in front of the real library. */
+/* Profiling shim — NOT part of the product, the tests or the bench, built by nothing in this repository, and NOT a
+ * CPU fallback: it computes no rollout at all (every payoff is the constant 1).  It exists so that the HOST-side cost of
+ * the batching adapter (include/pinyon_cuda/batcher.hh) can be profiled on a machine without a GPU:
+ *   gcc -O2 -shared -fPIC -I include -o /tmp/libfake.so tools/fake_gpu.c
+ *   LD_PRELOAD=/tmp/libfake.so tests/cpp/_bin/bench_search gpu_tb_batched 0 0 512 150 0 1 512
+ * (profiles/r3b_host_profile_batched_treebandit.txt). */
 #include <stdint.h>
 #include <stdlib.h>
 #include <string.h>
